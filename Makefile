@@ -1,0 +1,42 @@
+# Builds libgpushare_core.so (product), the oracle/test helpers and the fake NVML.
+# Everything lands in-tree so the built files travel to the GPU box with gpurun.
+NVCC      ?= nvcc
+CXX       ?= g++
+CC        ?= gcc
+PKG       := aliyun-gpushare-device-plugin_b200
+CSRC      := $(PKG)/csrc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVCCFLAGS := $(ARCH) -lineinfo -O3 -std=c++17 -Iinclude -I$(CSRC) -Xcompiler -fPIC,-fvisibility=hidden,-Wall
+CXXFLAGS  := -O2 -g -std=c++17 -fPIC -fvisibility=hidden -Wall -Wextra -Iinclude -I$(CSRC)
+CFLAGS    := -O2 -g -std=c11 -fPIC -Wall -Wextra
+
+CORE_SO   := $(PKG)/libgpushare_core.so
+CPP_SRCS  := $(wildcard $(CSRC)/*.cpp)
+CU_SRCS   := $(wildcard $(CSRC)/*.cu)
+OBJS      := $(CPP_SRCS:.cpp=.o) $(CU_SRCS:.cu=.o)
+
+ORACLE_SO := oracle/libgs_oracle.so
+FAKE_NVML := tests/fake_nvml/libfake_nvml.so
+
+all: $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML)
+
+$(CSRC)/%.o: $(CSRC)/%.cpp include/gpushare.h $(wildcard $(CSRC)/*.h)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+
+$(CSRC)/%.o: $(CSRC)/%.cu include/gpushare.h $(wildcard $(CSRC)/*.h)
+	$(NVCC) $(NVCCFLAGS) -c $< -o $@
+
+$(CORE_SO): $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -ldl -lpthread
+
+# Oracle: CPU restatement used ONLY by tests/, smoke() and bench.py's cpu_baseline leg.
+$(ORACLE_SO): $(wildcard oracle/*.c) $(wildcard oracle/*.cpp) $(wildcard oracle/*.h)
+	$(CXX) -O2 -g -std=c++17 -fPIC -Wall -Wextra -shared -o $@ $(wildcard oracle/*.cpp) -x c $(wildcard oracle/*.c) -lpthread
+
+$(FAKE_NVML): tests/fake_nvml/fake_nvml.c
+	$(CC) $(CFLAGS) -shared -o $@ $< -lpthread
+
+clean:
+	rm -f $(OBJS) $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML)
+
+.PHONY: all clean

@@ -1,0 +1,563 @@
+// probe.cu -- K1, the HBM slice probe (sm_100a). No counterpart in the reference:
+// cjg/aliyun-gpushare-device-plugin runs no GPU code.
+//
+// A batch of up to GS_PROBE_MAX_SLICES granted ranges is probed by two launches:
+//   probe_write_kernel : buf[i] = pattern(i, seed)       128-bit coalesced stores
+//   probe_verify_kernel: buf[i] == pattern(i, seed) ?    128-bit coalesced loads,
+//                        warp-ballot reduction, atomics only on the error path
+// Work is cut into 64 KiB tiles laid end to end over all slices of the batch; a
+// persistent grid (SMs x resident CTAs) strides over the tiles, so one launch
+// serves one 40 GiB slice or 64 small tenants equally well. Slice descriptors
+// travel as kernel parameters (no host->device copy); the only device memory
+// beyond the probed ranges is the per-slice result table.
+//
+// Algorithmic traffic: 1 byte stored + 1 byte loaded per slice byte.
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "gpushare.h"
+#include "internal.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr uint32_t kTileVec = 4096;  // 16-byte words per tile = 64 KiB
+
+struct SliceDesc {
+  uint4 *base;
+  uint64_t n_vec;       // 16-byte words in the slice
+  uint64_t tile_begin;  // first tile of this slice in the batch's tile space
+  uint64_t tile_end;    // one past its last tile
+  uint32_t seed;
+  uint32_t pad;
+};
+
+struct Batch {
+  SliceDesc s[GS_PROBE_MAX_SLICES];
+  uint64_t total_tiles;
+  uint32_t n;
+  uint32_t pad;
+};
+
+// Device-side result row; converted to gs_slice_result on the host.
+struct DevResult {
+  unsigned long long mismatches;
+  unsigned long long inv_first_bad;  // max over ~byte_offset; 0 = none (memset-able)
+  unsigned long long bit_flips;
+  unsigned long long reserved;
+};
+
+// pattern(i, seed): i = index of the 16-byte word inside the slice. Every output
+// word depends on every bit of i and of seed; word 1 is the complement of word 0
+// so each bit position is exercised in both polarities. Restated on the CPU in
+// oracle/pattern.c (test infrastructure only).
+__device__ __forceinline__ uint4 slice_pattern(uint64_t i, uint32_t seed) {
+  const uint32_t lo = (uint32_t)i;
+  const uint32_t hi = (uint32_t)(i >> 32);
+  uint32_t h = lo * 0x9E3779B1u + (hi ^ seed) * 0x85EBCA77u + seed;
+  h ^= h >> 15;
+  h *= 0x2C1B3C6Du;
+  h ^= h >> 12;
+  uint4 v;
+  v.x = h;
+  v.y = ~h;
+  v.z = h * 0x297A2D39u + lo;
+  v.w = __funnelshift_l(h, h, 13) ^ hi ^ 0xC2B2AE3Du;
+  return v;
+}
+
+// ---- 128-bit global accesses, one PTX form per variant ----------------------
+template <int V>
+__device__ __forceinline__ void st128(uint4 *p, const uint4 &v, uint64_t policy) {
+  if constexpr (V == 1) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x),
+                 "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+  } else if constexpr (V == 2) {
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+  } else if constexpr (V == 3) {
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(policy)
+                 : "memory");
+  } else {
+    asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x),
+                 "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+  }
+}
+
+template <int V>
+__device__ __forceinline__ uint4 ld128(const uint4 *p, uint64_t policy) {
+  uint4 r;
+  if constexpr (V == 1) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+  } else if constexpr (V == 2) {
+    asm volatile("ld.global.cs.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+  } else if constexpr (V == 3) {
+    asm volatile(
+        "ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+        : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+        : "l"(p), "l"(policy));
+  } else if constexpr (V == 4) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+  } else {
+    asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+  }
+  return r;
+}
+
+__device__ __forceinline__ uint64_t evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+
+// ---- store pass --------------------------------------------------------------
+template <int U, int V>
+__global__ void __launch_bounds__(kThreads)
+    probe_write_kernel(const __grid_constant__ Batch b) {
+  uint64_t policy = 0;
+  if constexpr (V == 3) policy = evict_first_policy();
+  uint32_t cur = 0;
+  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
+    while (tile >= b.s[cur].tile_end) ++cur;
+    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
+    const uint64_t rem = b.s[cur].n_vec - v0;
+    const uint32_t seed = b.s[cur].seed;
+    uint4 *p = b.s[cur].base + v0;
+    if (rem >= kTileVec) {
+#pragma unroll 1
+      for (uint32_t k = 0; k < kTileVec; k += kThreads * U) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const uint32_t j = k + u * kThreads + threadIdx.x;
+          st128<V>(p + j, slice_pattern(v0 + j, seed), policy);
+        }
+      }
+    } else {
+      for (uint32_t j = threadIdx.x; j < (uint32_t)rem; j += kThreads)
+        st128<V>(p + j, slice_pattern(v0 + j, seed), policy);
+    }
+  }
+}
+
+// ---- load + compare pass -----------------------------------------------------
+__device__ __forceinline__ bool differs(const uint4 &a, const uint4 &b) {
+  return ((a.x ^ b.x) | (a.y ^ b.y) | (a.z ^ b.z) | (a.w ^ b.w)) != 0u;
+}
+
+// Error path: every lane of the warp calls this with its own verdict. One lane
+// (the one holding the lowest bad address) issues the atomics for the warp.
+__device__ __noinline__ void report_warp(DevResult *res, bool bad, uint4 got, uint4 want,
+                                         uint64_t vec_index) {
+  const unsigned m = __ballot_sync(0xffffffffu, bad);
+  if (m == 0u) return;
+  unsigned flips = 0;
+  if (bad)
+    flips = __popc(got.x ^ want.x) + __popc(got.y ^ want.y) + __popc(got.z ^ want.z) +
+            __popc(got.w ^ want.w);
+  flips = __reduce_add_sync(0xffffffffu, flips);
+  const unsigned leader = __ffs(m) - 1;
+  if ((threadIdx.x & 31u) == leader) {
+    uint32_t d = got.x ^ want.x, word = 0;
+    if (d == 0u) { d = got.y ^ want.y; word = 1; }
+    if (d == 0u) { d = got.z ^ want.z; word = 2; }
+    if (d == 0u) { d = got.w ^ want.w; word = 3; }
+    const uint64_t byte_off = vec_index * 16ull + word * 4u + ((__ffs(d) - 1) >> 3);
+    atomicAdd(&res->mismatches, (unsigned long long)__popc(m));
+    atomicAdd(&res->bit_flips, (unsigned long long)flips);
+    atomicMax(&res->inv_first_bad, ~(unsigned long long)byte_off);
+  }
+}
+
+template <int U, int V>
+__global__ void __launch_bounds__(kThreads)
+    probe_verify_kernel(const __grid_constant__ Batch b, DevResult *__restrict__ results) {
+  uint64_t policy = 0;
+  if constexpr (V == 3) policy = evict_first_policy();
+  uint32_t cur = 0;
+  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
+    while (tile >= b.s[cur].tile_end) ++cur;
+    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
+    const uint64_t rem = b.s[cur].n_vec - v0;
+    const uint32_t seed = b.s[cur].seed;
+    const uint4 *p = b.s[cur].base + v0;
+    if (rem >= kTileVec) {
+#pragma unroll 1
+      for (uint32_t k = 0; k < kTileVec; k += kThreads * U) {
+        uint4 got[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)  // all loads in flight before any compare
+          got[u] = ld128<V>(p + k + u * kThreads + threadIdx.x, policy);
+        bool any = false;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const uint32_t j = k + u * kThreads + threadIdx.x;
+          any |= differs(got[u], slice_pattern(v0 + j, seed));
+        }
+        if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const uint32_t j = k + u * kThreads + threadIdx.x;
+            const uint4 want = slice_pattern(v0 + j, seed);
+            report_warp(results + cur, differs(got[u], want), got[u], want, v0 + j);
+          }
+        }
+      }
+    } else {
+      // ragged last tile of a slice: bounds as a predicate so the warp stays whole
+      const uint32_t r = (uint32_t)rem;
+      for (uint32_t k = 0; k < r; k += kThreads) {
+        const uint32_t j = k + threadIdx.x;
+        const bool inb = j < r;
+        const uint4 want = slice_pattern(v0 + j, seed);
+        const uint4 got = inb ? ld128<V>(p + j, policy) : want;
+        const bool bad = differs(got, want);
+        if (__any_sync(0xffffffffu, bad)) report_warp(results + cur, bad, got, want, v0 + j);
+      }
+    }
+  }
+}
+
+__global__ void probe_inject_kernel(uint32_t *word, uint32_t mask) { *word ^= mask; }
+
+// ---- variant dispatch ----------------------------------------------------------
+using WriteFn = void (*)(const Batch);
+using VerifyFn = void (*)(const Batch, DevResult *);
+
+constexpr int kNumWriteVariants = 4;
+constexpr int kNumVerifyVariants = 5;
+constexpr int kNumUnrolls = 3;  // U = 2, 4, 8 -> variant index / 10 selects
+
+template <int U>
+WriteFn write_fn_u(int v) {
+  switch (v) {
+    case 1: return probe_write_kernel<U, 1>;
+    case 2: return probe_write_kernel<U, 2>;
+    case 3: return probe_write_kernel<U, 3>;
+    default: return probe_write_kernel<U, 0>;
+  }
+}
+template <int U>
+VerifyFn verify_fn_u(int v) {
+  switch (v) {
+    case 1: return probe_verify_kernel<U, 1>;
+    case 2: return probe_verify_kernel<U, 2>;
+    case 3: return probe_verify_kernel<U, 3>;
+    case 4: return probe_verify_kernel<U, 4>;
+    default: return probe_verify_kernel<U, 0>;
+  }
+}
+// variant code = unroll_sel * 10 + access form; unroll_sel 0 -> U=4, 1 -> U=2, 2 -> U=8
+WriteFn write_fn(int code) {
+  const int v = code % 10, us = code / 10;
+  if (us == 1) return write_fn_u<2>(v);
+  if (us == 2) return write_fn_u<8>(v);
+  return write_fn_u<4>(v);
+}
+VerifyFn verify_fn(int code) {
+  const int v = code % 10, us = code / 10;
+  if (us == 1) return verify_fn_u<2>(v);
+  if (us == 2) return verify_fn_u<8>(v);
+  return verify_fn_u<4>(v);
+}
+bool valid_code(int code, int n_forms) {
+  return code >= 0 && code / 10 < kNumUnrolls && code % 10 < n_forms;
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+
+struct gs_probe {
+  int dev = 0;
+  int sms = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  DevResult *d_res = nullptr;
+  DevResult *h_res = nullptr;  // pinned
+  uint32_t pending_n = 0;
+  uint32_t pending_passes = 0;
+  uint32_t pending_launches = 0;
+  uint64_t pending_bytes = 0;
+  bool pending = false;
+  int write_variant = 0;
+  int verify_variant = 1;
+  int ctas_per_sm = 0;  // 0 = occupancy query
+};
+
+#define GS_CUDA(call)                                      \
+  do {                                                     \
+    cudaError_t e_ = (call);                               \
+    if (e_ != cudaSuccess) {                               \
+      gs_internal::set_cuda_error(#call, (int)e_, cudaGetErrorString(e_)); \
+      return GS_E_CUDA;                                    \
+    }                                                      \
+  } while (0)
+
+extern "C" {
+
+int gs_probe_open(int cuda_ordinal, gs_probe **out) {
+  if (!out || cuda_ordinal < 0) return GS_E_INVAL;
+  *out = nullptr;
+  int count = 0;
+  GS_CUDA(cudaGetDeviceCount(&count));
+  if (cuda_ordinal >= count) return GS_E_NOTFOUND;
+  DeviceGuard g(cuda_ordinal);
+  if (!g.ok) {
+    gs_internal::set_cuda_error("cudaSetDevice", -1, "cannot select device");
+    return GS_E_CUDA;
+  }
+  gs_probe *p = new (std::nothrow) gs_probe();
+  if (!p) return GS_E_INVAL;
+  p->dev = cuda_ordinal;
+  cudaError_t e = cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, cuda_ordinal);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
+  if (e == cudaSuccess) e = cudaMalloc(&p->d_res, sizeof(DevResult) * GS_PROBE_MAX_SLICES);
+  if (e == cudaSuccess) e = cudaMallocHost(&p->h_res, sizeof(DevResult) * GS_PROBE_MAX_SLICES);
+  if (e != cudaSuccess) {
+    gs_internal::set_cuda_error("gs_probe_open", (int)e, cudaGetErrorString(e));
+    gs_probe_close(p);
+    return GS_E_CUDA;
+  }
+  *out = p;
+  return GS_OK;
+}
+
+int gs_probe_close(gs_probe *p) {
+  if (!p) return GS_E_INVAL;
+  DeviceGuard g(p->dev);
+  if (p->stream) cudaStreamSynchronize(p->stream);
+  if (p->d_res) cudaFree(p->d_res);
+  if (p->h_res) cudaFreeHost(p->h_res);
+  for (auto &e : p->ev)
+    if (e) cudaEventDestroy(e);
+  if (p->stream) cudaStreamDestroy(p->stream);
+  delete p;
+  return GS_OK;
+}
+
+int gs_probe_sm_count(const gs_probe *p, int *sms) {
+  if (!p || !sms) return GS_E_INVAL;
+  *sms = p->sms;
+  return GS_OK;
+}
+
+int gs_probe_mem_alloc(gs_probe *p, uint64_t bytes, void **dptr) {
+  if (!p || !dptr || bytes == 0) return GS_E_INVAL;
+  DeviceGuard g(p->dev);
+  GS_CUDA(cudaMalloc(dptr, bytes));
+  return GS_OK;
+}
+
+int gs_probe_mem_free(gs_probe *p, void *dptr) {
+  if (!p) return GS_E_INVAL;
+  DeviceGuard g(p->dev);
+  GS_CUDA(cudaFree(dptr));
+  return GS_OK;
+}
+
+int gs_probe_mem_info(gs_probe *p, uint64_t *free_bytes, uint64_t *total_bytes) {
+  if (!p) return GS_E_INVAL;
+  DeviceGuard g(p->dev);
+  size_t f = 0, t = 0;
+  GS_CUDA(cudaMemGetInfo(&f, &t));
+  if (free_bytes) *free_bytes = f;
+  if (total_bytes) *total_bytes = t;
+  return GS_OK;
+}
+
+int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
+                         int ctas_per_sm) {
+  if (!p) return GS_E_INVAL;
+  if (write_variant >= 0) {
+    if (!valid_code(write_variant, kNumWriteVariants)) return GS_E_INVAL;
+    p->write_variant = write_variant;
+  }
+  if (verify_variant >= 0) {
+    if (!valid_code(verify_variant, kNumVerifyVariants)) return GS_E_INVAL;
+    p->verify_variant = verify_variant;
+  }
+  if (ctas_per_sm >= 0) {
+    if (ctas_per_sm > 32) return GS_E_INVAL;
+    p->ctas_per_sm = ctas_per_sm;
+  }
+  return GS_OK;
+}
+
+static int grid_for(const gs_probe *p, const void *fn, uint64_t total_tiles, int *grid) {
+  int per_sm = p->ctas_per_sm;
+  if (per_sm <= 0) {
+    GS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kThreads, 0));
+    if (per_sm < 1) per_sm = 1;
+  }
+  uint64_t g = (uint64_t)p->sms * (uint64_t)per_sm;
+  if (g > total_tiles) g = total_tiles;
+  *grid = (int)g;
+  return GS_OK;
+}
+
+int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t passes) {
+  if (!p || !slices || n == 0 || (passes & ~(GS_PROBE_WRITE | GS_PROBE_VERIFY)) || passes == 0)
+    return GS_E_INVAL;
+  if (n > GS_PROBE_MAX_SLICES) return GS_E_LIMIT;
+  if (p->pending) return GS_E_STATE;
+  Batch b;
+  memset(&b, 0, sizeof(b));
+  uint64_t tiles = 0, bytes = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const gs_slice &s = slices[i];
+    if (!s.base || s.bytes == 0 || (s.bytes & 15u) || ((uintptr_t)s.base & 15u)) return GS_E_INVAL;
+    SliceDesc &d = b.s[i];
+    d.base = (uint4 *)s.base;
+    d.n_vec = s.bytes / 16;
+    d.tile_begin = tiles;
+    tiles += (d.n_vec + kTileVec - 1) / kTileVec;
+    d.tile_end = tiles;
+    d.seed = s.seed;
+    bytes += s.bytes;
+  }
+  b.total_tiles = tiles;
+  b.n = n;
+
+  DeviceGuard g(p->dev);
+  uint32_t launches = 0;
+  GS_CUDA(cudaMemsetAsync(p->d_res, 0, sizeof(DevResult) * n, p->stream));
+  GS_CUDA(cudaEventRecord(p->ev[0], p->stream));
+  if (passes & GS_PROBE_WRITE) {
+    WriteFn fn = write_fn(p->write_variant);
+    int grid = 0;
+    int rc = grid_for(p, (const void *)fn, tiles, &grid);
+    if (rc != GS_OK) return rc;
+    fn<<<grid, kThreads, 0, p->stream>>>(b);
+    GS_CUDA(cudaGetLastError());
+    ++launches;
+  }
+  GS_CUDA(cudaEventRecord(p->ev[1], p->stream));
+  if (passes & GS_PROBE_VERIFY) {
+    VerifyFn fn = verify_fn(p->verify_variant);
+    int grid = 0;
+    int rc = grid_for(p, (const void *)fn, tiles, &grid);
+    if (rc != GS_OK) return rc;
+    fn<<<grid, kThreads, 0, p->stream>>>(b, p->d_res);
+    GS_CUDA(cudaGetLastError());
+    ++launches;
+  }
+  GS_CUDA(cudaEventRecord(p->ev[2], p->stream));
+  GS_CUDA(cudaMemcpyAsync(p->h_res, p->d_res, sizeof(DevResult) * n, cudaMemcpyDeviceToHost,
+                          p->stream));
+  GS_CUDA(cudaEventRecord(p->ev[3], p->stream));
+  p->pending = true;
+  p->pending_n = n;
+  p->pending_passes = passes;
+  p->pending_bytes = bytes;
+  p->pending_launches = launches;
+  return GS_OK;
+}
+
+int gs_probe_poll(gs_probe *p) {
+  if (!p) return GS_E_INVAL;
+  if (!p->pending) return GS_OK;
+  DeviceGuard g(p->dev);
+  cudaError_t e = cudaEventQuery(p->ev[3]);
+  if (e == cudaSuccess) return GS_OK;
+  if (e == cudaErrorNotReady) return GS_E_TIMEOUT;
+  gs_internal::set_cuda_error("cudaEventQuery", (int)e, cudaGetErrorString(e));
+  return GS_E_CUDA;
+}
+
+int gs_probe_wait(gs_probe *p, gs_slice_result *results, uint32_t n, gs_probe_timing *timing) {
+  if (!p) return GS_E_INVAL;
+  if (!p->pending) return GS_E_STATE;
+  if (results && n < p->pending_n) return GS_E_NOSPACE;
+  DeviceGuard g(p->dev);
+  p->pending = false;
+  GS_CUDA(cudaEventSynchronize(p->ev[3]));
+  if (results) {
+    for (uint32_t i = 0; i < p->pending_n; ++i) {
+      const DevResult &r = p->h_res[i];
+      results[i].mismatches = r.mismatches;
+      results[i].first_bad_byte = r.mismatches ? ~r.inv_first_bad : UINT64_MAX;
+      results[i].bit_flips = r.bit_flips;
+      results[i].reserved = 0;
+    }
+  }
+  if (timing) {
+    memset(timing, 0, sizeof(*timing));
+    if (p->pending_passes & GS_PROBE_WRITE)
+      GS_CUDA(cudaEventElapsedTime(&timing->write_ms, p->ev[0], p->ev[1]));
+    if (p->pending_passes & GS_PROBE_VERIFY)
+      GS_CUDA(cudaEventElapsedTime(&timing->verify_ms, p->ev[1], p->ev[2]));
+    timing->bytes = p->pending_bytes;
+    timing->launches = p->pending_launches;
+  }
+  return GS_OK;
+}
+
+int gs_probe_run(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t passes,
+                 gs_slice_result *results, gs_probe_timing *timing) {
+  int rc = gs_probe_submit(p, slices, n, passes);
+  if (rc != GS_OK) return rc;
+  return gs_probe_wait(p, results, n, timing);
+}
+
+int gs_probe_run_granted(int cuda_ordinal, uint64_t bytes, uint32_t seed,
+                         gs_slice_result *result, gs_probe_timing *timing) {
+  if (bytes == 0 || (bytes & 15u)) return GS_E_INVAL;
+  gs_probe *p = nullptr;
+  int rc = gs_probe_open(cuda_ordinal, &p);
+  if (rc != GS_OK) return rc;
+  void *d = nullptr;
+  rc = gs_probe_mem_alloc(p, bytes, &d);
+  if (rc == GS_OK) {
+    gs_slice s{d, bytes, seed, 0};
+    rc = gs_probe_run(p, &s, 1, GS_PROBE_WRITE | GS_PROBE_VERIFY, result, timing);
+    gs_probe_mem_free(p, d);
+  }
+  gs_probe_close(p);
+  return rc;
+}
+
+int gs_probe_inject(gs_probe *p, void *base, uint64_t byte_offset, uint32_t mask) {
+  if (!p || !base || (byte_offset & 3u)) return GS_E_INVAL;
+  if (p->pending) return GS_E_STATE;
+  DeviceGuard g(p->dev);
+  probe_inject_kernel<<<1, 1, 0, p->stream>>>((uint32_t *)((char *)base + byte_offset), mask);
+  GS_CUDA(cudaGetLastError());
+  GS_CUDA(cudaStreamSynchronize(p->stream));
+  return GS_OK;
+}
+
+int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t bytes) {
+  if (!p || !dptr || !host) return GS_E_INVAL;
+  DeviceGuard g(p->dev);
+  GS_CUDA(cudaStreamSynchronize(p->stream));
+  GS_CUDA(cudaMemcpy(host, dptr, bytes, cudaMemcpyDeviceToHost));
+  return GS_OK;
+}
+
+}  // extern "C"

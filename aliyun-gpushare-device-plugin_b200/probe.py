@@ -1,0 +1,125 @@
+"""Slice probe (K1) -- thin object wrapper over the gs_probe_* C ABI.
+
+No counterpart in the reference (it runs no GPU code); see include/gpushare.h.
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+from . import _lib as L
+
+
+@dataclass
+class SliceVerdict:
+    mismatches: int
+    first_bad_byte: int  # 2**64-1 when clean
+    bit_flips: int
+
+    @property
+    def clean(self):
+        return self.mismatches == 0
+
+
+@dataclass
+class Timing:
+    write_ms: float
+    verify_ms: float
+    bytes: int
+    launches: int
+
+    def gbps(self):
+        """2 algorithmic bytes per slice byte over both passes (SURVEY 8(d) metric 3)."""
+        t = self.write_ms + self.verify_ms
+        n = (self.write_ms > 0) + (self.verify_ms > 0)
+        return n * self.bytes / (t * 1e-3) / 1e9 if t > 0 else 0.0
+
+
+class Probe:
+    """One probe engine (stream, events, result table) bound to one CUDA ordinal."""
+
+    def __init__(self, cuda_ordinal=0):
+        self.lib = L.load()
+        h = C.c_void_p()
+        L.check(self.lib.gs_probe_open(cuda_ordinal, C.byref(h)), "gs_probe_open")
+        self.h = h
+        self.ordinal = cuda_ordinal
+        self._n = 0
+
+    def close(self):
+        if self.h:
+            self.lib.gs_probe_close(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def sm_count(self):
+        v = C.c_int()
+        L.check(self.lib.gs_probe_sm_count(self.h, C.byref(v)))
+        return v.value
+
+    def mem_info(self):
+        f, t = C.c_uint64(), C.c_uint64()
+        L.check(self.lib.gs_probe_mem_info(self.h, C.byref(f), C.byref(t)), "gs_probe_mem_info")
+        return f.value, t.value
+
+    def alloc(self, nbytes):
+        p = C.c_void_p()
+        L.check(self.lib.gs_probe_mem_alloc(self.h, nbytes, C.byref(p)), "gs_probe_mem_alloc")
+        return p.value
+
+    def free(self, dptr):
+        L.check(self.lib.gs_probe_mem_free(self.h, C.c_void_p(dptr)), "gs_probe_mem_free")
+
+    def set_variant(self, write=-1, verify=-1, ctas_per_sm=-1):
+        L.check(self.lib.gs_probe_set_variant(self.h, write, verify, ctas_per_sm),
+                "gs_probe_set_variant")
+
+    @staticmethod
+    def _slices(slices):
+        arr = (L.Slice * len(slices))()
+        for i, s in enumerate(slices):
+            base, nbytes, seed = s[0], s[1], s[2]
+            arr[i] = L.Slice(base, nbytes, seed, s[3] if len(s) > 3 else i)
+        return arr
+
+    def submit(self, slices, passes=L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY):
+        arr = self._slices(slices)
+        L.check(self.lib.gs_probe_submit(self.h, arr, len(slices), passes), "gs_probe_submit")
+        self._n = len(slices)
+
+    def wait(self):
+        res = (L.SliceResult * self._n)()
+        tm = L.ProbeTiming()
+        L.check(self.lib.gs_probe_wait(self.h, res, self._n, C.byref(tm)), "gs_probe_wait")
+        return ([SliceVerdict(r.mismatches, r.first_bad_byte, r.bit_flips) for r in res],
+                Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches))
+
+    def idle(self):
+        return self.lib.gs_probe_poll(self.h) == L.GS_OK
+
+    def run(self, slices, passes=L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY):
+        self.submit(slices, passes)
+        return self.wait()
+
+    def inject(self, base, byte_offset, mask):
+        L.check(self.lib.gs_probe_inject(self.h, C.c_void_p(base), byte_offset, mask),
+                "gs_probe_inject")
+
+    def read(self, dptr, nbytes):
+        buf = (C.c_uint8 * nbytes)()
+        L.check(self.lib.gs_probe_read(self.h, C.c_void_p(dptr), buf, nbytes), "gs_probe_read")
+        return bytes(buf)
+
+
+def run_granted(cuda_ordinal, nbytes, seed):
+    """Allocate exactly `nbytes` on the GPU, probe it, free it (gs_probe_run_granted)."""
+    lib = L.load()
+    res, tm = L.SliceResult(), L.ProbeTiming()
+    L.check(lib.gs_probe_run_granted(cuda_ordinal, nbytes, seed, C.byref(res), C.byref(tm)),
+            "gs_probe_run_granted")
+    return (SliceVerdict(res.mismatches, res.first_bad_byte, res.bit_flips),
+            Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches))
