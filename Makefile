@@ -6,9 +6,10 @@ CC        ?= gcc
 PKG       := aliyun-gpushare-device-plugin_b200
 CSRC      := $(PKG)/csrc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
+CUDA_INC  ?= /usr/local/cuda/include
 NVCCFLAGS := $(ARCH) -lineinfo -O3 -std=c++17 -Iinclude -I$(CSRC) -Xcompiler -fPIC,-fvisibility=hidden,-Wall
-CXXFLAGS  := -O2 -g -std=c++17 -fPIC -fvisibility=hidden -Wall -Wextra -Iinclude -I$(CSRC)
-CFLAGS    := -O2 -g -std=c11 -fPIC -Wall -Wextra
+CXXFLAGS  := -O2 -g -std=c++17 -fPIC -fvisibility=hidden -Wall -Wextra -Iinclude -I$(CSRC) -I$(CUDA_INC)
+CFLAGS    := -O2 -g -std=gnu11 -fPIC -Wall -Wextra
 
 CORE_SO   := $(PKG)/libgpushare_core.so
 CPP_SRCS  := $(wildcard $(CSRC)/*.cpp)
@@ -30,13 +31,18 @@ $(CORE_SO): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -ldl -lpthread
 
 # Oracle: CPU restatement used ONLY by tests/, smoke() and bench.py's cpu_baseline leg.
-$(ORACLE_SO): $(wildcard oracle/*.c) $(wildcard oracle/*.cpp) $(wildcard oracle/*.h)
-	$(CXX) -O2 -g -std=c++17 -fPIC -Wall -Wextra -shared -o $@ $(wildcard oracle/*.cpp) -x c $(wildcard oracle/*.c) -lpthread
+ORACLE_OBJS := $(patsubst %.c,%.o,$(wildcard oracle/*.c)) $(patsubst %.cpp,%.o,$(wildcard oracle/*.cpp))
+oracle/%.o: oracle/%.c
+	$(CC) $(CFLAGS) -c $< -o $@
+oracle/%.o: oracle/%.cpp $(wildcard oracle/*.h)
+	$(CXX) -O2 -g -std=c++17 -fPIC -Wall -Wextra -c $< -o $@
+$(ORACLE_SO): $(ORACLE_OBJS)
+	$(CXX) -shared -o $@ $(ORACLE_OBJS) -lpthread
 
 $(FAKE_NVML): tests/fake_nvml/fake_nvml.c
 	$(CC) $(CFLAGS) -shared -o $@ $< -lpthread
 
 clean:
-	rm -f $(OBJS) $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML)
+	rm -f $(OBJS) $(CORE_SO) $(ORACLE_OBJS) $(ORACLE_SO) $(FAKE_NVML)
 
 .PHONY: all clean

@@ -41,7 +41,7 @@ class Str(C.Structure):
 
 class PodView(C.Structure):
     _fields_ = [("uid", Str), ("ns", Str), ("name", Str), ("node_name", Str),
-                ("gpu_mem_limit", C.c_uint64), ("n_annotations", C.c_uint32),
+                ("gpu_mem_limit", C.c_uint64),
                 ("ann_idx", Str), ("ann_assume_time", Str), ("ann_assigned", Str)]
 
 
@@ -149,6 +149,7 @@ SIGNATURES = {
     "gs_probe_inject": (_int, [_vp, _vp, _u64, _u32]),
     "gs_probe_read": (_int, [_vp, _vp, _vp, _u64]),
     "gs_probe_set_variant": (_int, [_vp, _int, _int, _int]),
+    "gs_probe_set_write_rate": (_int, [_vp, _u32]),
 }
 
 _lib = None

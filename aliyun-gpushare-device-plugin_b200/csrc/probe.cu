@@ -2,7 +2,10 @@
 // cjg/aliyun-gpushare-device-plugin runs no GPU code.
 //
 // A batch of up to GS_PROBE_MAX_SLICES granted ranges is probed by two launches:
-//   probe_write_kernel : buf[i] = pattern(i, seed)       128-bit coalesced stores
+//   probe_write_bulk_kernel (default) : pattern(i, seed) -> shared memory (128-bit
+//                        STS), then cp.async.bulk (TMA engine) full-line stores
+//   probe_write_kernel : buf[i] = pattern(i, seed)       128-bit coalesced STG
+//                        (selectable; tops out ~15% lower)
 //   probe_verify_kernel: buf[i] == pattern(i, seed) ?    128-bit coalesced loads,
 //                        warp-ballot reduction, atomics only on the error path
 // Work is cut into 64 KiB tiles laid end to end over all slices of the batch; a
@@ -154,6 +157,77 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// ---- store pass through the TMA engine ----------------------------------------
+// Plain STG.128 stores plateau near 6.3 TB/s on B200; the same bytes sent as bulk
+// asynchronous shared->global copies reach the rate the copy engine's memset gets
+// (7.4 TB/s). One CTA per SM owns a ring of STAGES 64 KiB tiles in shared memory:
+// all threads fill a tile with the pattern (conflict-free 128-bit STS), then the
+// first kTileVec/sub_vec threads each issue one bulk store of sub_vec words.
+//
+// Pacing. B200's write path degrades when it is offered more than it can drain:
+// unpaced, this kernel (like plain STG) settles near 6.4 TB/s, while the same
+// stores offered at just under the drain rate sustain 7.3+ TB/s (measured; see
+// DESIGN.md "write pacing"). So each CTA runs a token bucket on %globaltimer
+// (32 ns steps on B200): one tile per period_x16/16 ns, never bursting to catch
+// up. period_x16 == 0 disables pacing.
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+template <int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+    probe_write_bulk_kernel(const __grid_constant__ Batch b, uint32_t sub_vec,
+                            uint32_t period_x16) {
+  extern __shared__ __align__(128) uint4 ring[];
+  const uint32_t nsub = kTileVec / sub_vec;
+  uint32_t cur = 0;
+  int stage = 0;
+  uint64_t next_x16 = period_x16 ? global_timer_ns() * 16 : 0;
+  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
+    while (tile >= b.s[cur].tile_end) ++cur;
+    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
+    const uint64_t rem64 = b.s[cur].n_vec - v0;
+    const uint32_t rem = rem64 >= kTileVec ? kTileVec : (uint32_t)rem64;
+    const uint32_t seed = b.s[cur].seed;
+    uint4 *buf = ring + (size_t)stage * kTileVec;
+    // the bulk store that last read this stage must have drained shared memory
+    if (threadIdx.x < nsub)
+      asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(STAGES - 1) : "memory");
+    __syncthreads();
+    if (rem == kTileVec) {
+#pragma unroll 4
+      for (uint32_t j = threadIdx.x; j < kTileVec; j += kThreads)
+        buf[j] = slice_pattern(v0 + j, seed);
+    } else {
+      for (uint32_t j = threadIdx.x; j < rem; j += kThreads) buf[j] = slice_pattern(v0 + j, seed);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < nsub) {
+      if (period_x16) {
+        uint64_t now;
+        while ((now = global_timer_ns() * 16) < next_x16) {
+        }
+        if (now > next_x16 + period_x16) next_x16 = now;  // late: do not burst
+        next_x16 += period_x16;
+      }
+      const uint32_t first = threadIdx.x * sub_vec;
+      if (first < rem) {
+        const uint32_t cnt = rem - first < sub_vec ? rem - first : sub_vec;
+        const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf + first);
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                         b.s[cur].base + v0 + first),
+                     "r"(saddr), "r"(cnt * 16u)
+                     : "memory");
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    stage = stage + 1 == STAGES ? 0 : stage + 1;
+  }
+  if (threadIdx.x < nsub) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 // ---- load + compare pass -----------------------------------------------------
 __device__ __forceinline__ bool differs(const uint4 &a, const uint4 &b) {
   return ((a.x ^ b.x) | (a.y ^ b.y) | (a.z ^ b.z) | (a.w ^ b.w)) != 0u;
@@ -238,7 +312,19 @@ __global__ void probe_inject_kernel(uint32_t *word, uint32_t mask) { *word ^= ma
 using WriteFn = void (*)(const Batch);
 using VerifyFn = void (*)(const Batch, DevResult *);
 
-constexpr int kNumWriteVariants = 4;
+constexpr int kNumWriteVariants = 4;  // STG forms (codes 0..29)
+// Bulk-store codes: 100 + 10 * stages_sel + sub_sel
+//   stages_sel 0 -> 3-stage ring (192 KiB smem), 1 -> 2-stage ring (128 KiB)
+//   sub_sel    0 -> 4 KiB bulk ops, 1 -> 2 KiB, 2 -> 8 KiB, 3 -> 16 KiB, 4 -> 1 KiB
+constexpr int kWriteBulkBase = 100;
+constexpr int kDefaultWriteVariant = kWriteBulkBase + 2;  // 3-stage ring, 8 KiB bulk ops
+// aggregate offered store rate the token buckets add up to (GB/s == bytes/ns)
+constexpr uint32_t kDefaultWriteRateGBps = 7600;
+constexpr uint32_t kBulkSubVec[5] = {256, 128, 512, 1024, 64};
+bool is_bulk_code(int code) {
+  return code >= kWriteBulkBase && (code - kWriteBulkBase) / 10 < 2 &&
+         (code - kWriteBulkBase) % 10 < 5;
+}
 constexpr int kNumVerifyVariants = 5;
 constexpr int kNumUnrolls = 3;  // U = 2, 4, 8 -> variant index / 10 selects
 
@@ -304,9 +390,11 @@ struct gs_probe {
   uint32_t pending_launches = 0;
   uint64_t pending_bytes = 0;
   bool pending = false;
-  int write_variant = 0;
-  int verify_variant = 1;
-  int ctas_per_sm = 0;  // 0 = occupancy query
+  int write_variant = kDefaultWriteVariant;
+  bool bulk_attr_set[2] = {false, false};
+  uint32_t write_rate_gbps = kDefaultWriteRateGBps;  // 0 = unpaced
+  int verify_variant = 0;  // plain ld.global.v4: best when the pass follows a store pass
+  int ctas_per_sm = 8;     // STG/LDG kernels: CTAs per SM in the grid; 0 = occupancy query
 };
 
 #define GS_CUDA(call)                                      \
@@ -395,7 +483,8 @@ int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
                          int ctas_per_sm) {
   if (!p) return GS_E_INVAL;
   if (write_variant >= 0) {
-    if (!valid_code(write_variant, kNumWriteVariants)) return GS_E_INVAL;
+    if (!valid_code(write_variant, kNumWriteVariants) && !is_bulk_code(write_variant))
+      return GS_E_INVAL;
     p->write_variant = write_variant;
   }
   if (verify_variant >= 0) {
@@ -406,6 +495,13 @@ int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
     if (ctas_per_sm > 32) return GS_E_INVAL;
     p->ctas_per_sm = ctas_per_sm;
   }
+  return GS_OK;
+}
+
+int gs_probe_set_write_rate(gs_probe *p, uint32_t gbps) {
+  if (!p) return GS_E_INVAL;
+  if (gbps > 100000) return GS_E_INVAL;
+  p->write_rate_gbps = gbps;
   return GS_OK;
 }
 
@@ -448,7 +544,28 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
   uint32_t launches = 0;
   GS_CUDA(cudaMemsetAsync(p->d_res, 0, sizeof(DevResult) * n, p->stream));
   GS_CUDA(cudaEventRecord(p->ev[0], p->stream));
-  if (passes & GS_PROBE_WRITE) {
+  if ((passes & GS_PROBE_WRITE) && is_bulk_code(p->write_variant)) {
+    const int stages_sel = (p->write_variant - kWriteBulkBase) / 10;
+    const uint32_t sub_vec = kBulkSubVec[(p->write_variant - kWriteBulkBase) % 10];
+    const int stages = stages_sel == 0 ? 3 : 2;
+    const size_t smem = (size_t)stages * kTileVec * sizeof(uint4);
+    void (*fn)(const Batch, uint32_t, uint32_t) =
+        stages == 3 ? probe_write_bulk_kernel<3> : probe_write_bulk_kernel<2>;
+    if (!p->bulk_attr_set[stages_sel]) {
+      GS_CUDA(cudaFuncSetAttribute((const void *)fn,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      p->bulk_attr_set[stages_sel] = true;
+    }
+    // the ring fills an SM's shared memory: exactly one CTA per SM
+    const uint64_t grid = tiles < (uint64_t)p->sms ? tiles : (uint64_t)p->sms;
+    // per-CTA period so that `grid` CTAs together offer write_rate_gbps
+    uint32_t period_x16 = 0;
+    if (p->write_rate_gbps)
+      period_x16 = (uint32_t)((double)kTileVec * 16.0 * (double)grid / (double)p->write_rate_gbps * 16.0);
+    fn<<<(int)grid, kThreads, smem, p->stream>>>(b, sub_vec, period_x16);
+    GS_CUDA(cudaGetLastError());
+    ++launches;
+  } else if (passes & GS_PROBE_WRITE) {
     WriteFn fn = write_fn(p->write_variant);
     int grid = 0;
     int rc = grid_for(p, (const void *)fn, tiles, &grid);

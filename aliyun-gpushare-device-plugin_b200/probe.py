@@ -78,6 +78,9 @@ class Probe:
         L.check(self.lib.gs_probe_set_variant(self.h, write, verify, ctas_per_sm),
                 "gs_probe_set_variant")
 
+    def set_write_rate(self, gbps):
+        L.check(self.lib.gs_probe_set_write_rate(self.h, gbps), "gs_probe_set_write_rate")
+
     @staticmethod
     def _slices(slices):
         arr = (L.Slice * len(slices))()

@@ -201,7 +201,8 @@ typedef struct gs_pod_view {
   /* Sum over spec.containers of uint(Limits["aliyun.com/gpu-mem"].Value())
    * with Go's wrapping uint add (podutils.go:122-131); see gs_quantity_value. */
   uint64_t gpu_mem_limit;
-  uint32_t n_annotations;  /* len(metadata.annotations) (podutils.go:41)      */
+  /* podutils.go:41 guards on len(annotations) > 0; a pod that reaches that line
+   * was selected by its annotations, so the three values below carry it all.   */
   gs_str ann_idx;          /* ALIYUN_COM_GPU_MEM_IDX          (NULL = absent) */
   gs_str ann_assume_time;  /* ALIYUN_COM_GPU_MEM_ASSUME_TIME  (NULL = absent) */
   gs_str ann_assigned;     /* ALIYUN_COM_GPU_MEM_ASSIGNED     (NULL = absent) */
@@ -353,6 +354,9 @@ GS_API int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t byt
 /* Kernel variant selection for tuning; -1 keeps the default. */
 GS_API int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
                                 int ctas_per_sm);
+/* Offered rate (GB/s, whole GPU) the store pass paces itself to; 0 = unpaced.
+ * Default 7600: B200's write path sustains more when not over-offered.        */
+GS_API int gs_probe_set_write_rate(gs_probe *p, uint32_t gbps);
 /* Host restatement of the pattern is NOT here: it lives in oracle/pattern.c. */
 
 #ifdef __cplusplus

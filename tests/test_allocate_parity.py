@@ -1,0 +1,176 @@
+"""Allocate parity: the C ABI against the golden vectors and against the oracle.
+
+Envs are compared as decoded maps, never as wire bytes (H3); the patch body is
+compared byte for byte with the injected clock (H4).
+"""
+import random
+
+import pytest
+
+from gpushare_b200 import api
+from oracle import ref_model as R
+from tests.helpers import oracle_for_case, patch_body, product_for_case, product_step
+
+
+def test_product_matches_golden(golden_cases):
+    for c in golden_cases:
+        table, plug = product_for_case(c)
+        for k, st in enumerate(c["steps"]):
+            envs, kind, patched = product_step(c, table, plug, st["request"])
+            assert envs == st["expect_envs"], (c["name"], k, envs)
+            assert kind == st["expect_kind"], (c["name"], k, kind)
+            want = st["expect_patch"]["name"] if st["expect_patch"] else None
+            if c["fail_patch"] != "always":
+                assert patched == want, (c["name"], k)
+
+
+def test_patch_body_bytes(golden_cases):
+    c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
+    table, plug = product_for_case(c)
+    pods = [plug.get_pod(i) for i in range(plug.pod_count())]
+    d = api.allocate(table, c["node"], R.encode_allocate_request(c["steps"][0]["request"]), pods,
+                     c["clock"])
+    assert d.patch == c["steps"][0]["expect_patch"]["body"].encode() == patch_body(c["clock"])
+    d = api.allocate(table, c["node"], R.encode_allocate_request(c["steps"][0]["request"]), pods,
+                     -5)
+    assert d.patch == patch_body(-5)
+
+
+def test_patch_applied_to_pod_source(golden_cases):
+    c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
+    table, plug = product_for_case(c)
+    plug.Allocate(R.encode_allocate_request(c["steps"][0]["request"]))
+    p0 = plug.get_pod(0)
+    assert p0.ann_assigned == "true" and p0.ann_assume_time == str(c["clock"])
+    assert plug.get_pod(1).ann_assigned == "false"
+
+
+def _random_case(rng, n_pods, n_gpus, unit, ties):
+    node = "node-a"
+    times = [str(rng.randrange(1, 10**6)) for _ in range(n_pods)]
+    if ties:
+        times = [str(rng.randrange(1, max(2, n_pods // 3))) for _ in range(n_pods)]
+    pods = []
+    for k in range(n_pods):
+        ann = {}
+        r = rng.random()
+        if r < 0.85:
+            ann["ALIYUN_COM_GPU_MEM_IDX"] = rng.choice(
+                [str(rng.randrange(n_gpus)), str(rng.randrange(n_gpus)), "x", "-1", str(n_gpus),
+                 "+0", "01"])
+        if rng.random() < 0.9:
+            ann["ALIYUN_COM_GPU_MEM_ASSUME_TIME"] = rng.choice([times[k], times[k], times[k], "bad", ""])
+        if rng.random() < 0.92:
+            ann["ALIYUN_COM_GPU_MEM_ASSIGNED"] = rng.choice(["false"] * 6 + ["true", "False"])
+        limits = [rng.choice([1, 2, 2, 3, "4", "1500m", None]) for _ in range(rng.choice([1, 1, 2, 3]))]
+        containers = [{"name": "c%d" % i, "resources": ({} if l is None else
+                                                         {"limits": {"aliyun.com/gpu-mem": l}})}
+                      for i, l in enumerate(limits)]
+        pods.append({"metadata": {"uid": "u%d" % (k if rng.random() < 0.93 else rng.randrange(n_pods)),
+                                  "name": "p%d" % k, "namespace": rng.choice(["default", "team-b"]),
+                                  "annotations": ann},
+                     "spec": {"nodeName": rng.choice([node] * 9 + ["node-b"]), "containers": containers},
+                     "status": {"phase": "Pending"}})
+    gpus = [["GPU-%08x-0000-0000-0000-%012x" % (i, i), 16384] for i in range(n_gpus)]
+    return {"name": "rand", "gpus": gpus, "unit": unit, "node": node,
+            "cgpu_disable": rng.random() < 0.3, "clock": rng.randrange(1, 2**62), "pods": pods,
+            "fail_list": False, "fail_patch": None}
+
+
+def _random_request(rng, gpus):
+    reqs = []
+    for _ in range(rng.choice([1, 1, 1, 2, 3])):
+        n = rng.choice([0, 1, 2, 2, 3, 4, 5])
+        reqs.append(["%s-_-%d" % (rng.choice(gpus)[0], rng.randrange(16)) for _ in range(n)])
+    return reqs
+
+
+@pytest.mark.parametrize("n_pods,ties", [(0, False), (3, False), (8, True), (12, True),
+                                          (13, False), (40, False), (64, False), (200, False)])
+def test_random_sequences_match_oracle(n_pods, ties):
+    """Seeded random pod sets and request sequences: every response and every patch
+    target equals the oracle's. Tie order is only exercised for n <= 12 (H2)."""
+    rng = random.Random(20261106 + n_pods)
+    for trial in range(25 if n_pods <= 64 else 4):
+        c = _random_case(rng, n_pods, rng.choice([1, 2, 8]), rng.choice(["GiB", "MiB"]), ties)
+        table, plug = product_for_case(c)
+        src, oracle = oracle_for_case(c)
+        for step in range(min(2 * n_pods + 3, 40)):
+            reqs = _random_request(rng, c["gpus"])
+            before = len(src.patches)
+            want = oracle.Allocate(reqs)
+            envs, kind, patched = product_step(c, table, plug, reqs)
+            assert envs == want, (n_pods, trial, step, kind)
+            want_patched = src.patches[before][1] if len(src.patches) > before else None
+            assert patched == want_patched, (n_pods, trial, step)
+
+
+def test_ties_above_12_agree_with_oracle_port():
+    """n > 12 with equal assume times: product and oracle both follow the published
+    pdqsort, so they agree with each other; agreement with real Go is unpinned (H2)."""
+    rng = random.Random(7)
+    for n in (13, 20, 50, 64):
+        c = _random_case(rng, n, 8, "GiB", ties=True)
+        table, plug = product_for_case(c)
+        src, oracle = oracle_for_case(c)
+        for step in range(n):
+            reqs = [["x"] * rng.choice([1, 2, 3, 4])]
+            assert product_step(c, table, plug, reqs)[0] == oracle.Allocate(reqs), (n, step)
+
+
+def test_request_scan_and_malformed_wire():
+    reqs = [["a" * 44] * 1024, [], ["b" * 200, ""]]
+    wire = R.encode_allocate_request(reqs)
+    counts, total = api.request_scan(wire)
+    assert counts == [1024, 0, 2] and total == 1026
+    # unknown fields of every wire type are skipped, as a protobuf decoder would
+    extra = (b"\x10\x05" + b"\x19" + b"\0" * 8 + b"\x25" + b"\0" * 4 + b"\x1a\x03abc")
+    inner = b"\x0a\x01x" + b"\x10\x7f" + b"\x0a\x02yz"
+    wire2 = extra + b"\x0a" + bytes([len(inner)]) + inner
+    assert api.request_scan(wire2) == ([2], 2)
+    table = api.DeviceTable(["GPU-a"], 16, "GiB")
+    for bad in (b"\x0a\x05ab", b"\x0a", b"\x0a\x03\x0a\x05a", b"\x0b\x00", b"\xff" * 11):
+        with pytest.raises(api.L.GpushareError) as e:
+            api.allocate(table, "n", bad, [])
+        assert e.value.status == api.L.GS_E_WIRE
+
+
+def test_empty_request_no_containers():
+    table = api.DeviceTable(["GPU-a", "GPU-b"], 16, "GiB")
+    d = api.allocate(table, "n", b"", [])
+    assert d.response == b"" and d.n_containers == 0 and d.kind == "err-no-match"
+
+
+def test_response_buffer_too_small_reports_need():
+    import ctypes as C
+    lib = api.L.load()
+    table = api.DeviceTable(["GPU-a", "GPU-b"], 16, "GiB")
+    wire = R.encode_allocate_request([["x", "y"]])
+    keep = []
+    ctx = api.L.AllocCtx(table.h, api._str("n", keep), 0, 0)
+    res = api.L.AllocResult()
+    small = C.create_string_buffer(8)
+    patch = C.create_string_buffer(256)
+    rc = lib.gs_allocate(C.byref(ctx), wire, len(wire), None, 0, small, 8, patch, 256, C.byref(res))
+    assert rc == api.L.GS_E_NOSPACE and res.resp_len > 8
+    big = C.create_string_buffer(res.resp_len)
+    rc = lib.gs_allocate(C.byref(ctx), wire, len(wire), None, 0, big, res.resp_len, patch, 256,
+                         C.byref(res))
+    assert rc == api.L.GS_OK
+    assert R.decode_allocate_response(big.raw[:res.resp_len])[0]["ALIYUN_COM_GPU_MEM_IDX"] == "-1"
+
+
+def test_large_mib_request_counts():
+    """BASELINE config 3 sizes: 1 024 .. 40 960 ids per request at MiB granularity."""
+    rng = random.Random(1)
+    uuids = ["GPU-%08x-0000-0000-0000-%012x" % (i, i) for i in range(8)]
+    table = api.DeviceTable(uuids, 183359, "MiB")
+    for n in (1024, 4096, 16384, 40960):
+        ids = ["%s-_-%d" % (uuids[rng.randrange(8)], rng.randrange(183359)) for _ in range(n)]
+        wire = R.encode_allocate_request([ids])
+        pod = api.Pod("u", "default", "tenant", "n", n, "5", "1", "false")
+        d = api.allocate(table, "n", wire, [pod], 42)
+        envs = R.decode_allocate_response(d.response)
+        assert envs == [{"NVIDIA_VISIBLE_DEVICES": "5", "ALIYUN_COM_GPU_MEM_IDX": "5",
+                         "ALIYUN_COM_GPU_MEM_POD": str(n), "ALIYUN_COM_GPU_MEM_CONTAINER": str(n),
+                         "ALIYUN_COM_GPU_MEM_DEV": "183359"}]

@@ -1,0 +1,145 @@
+"""The oracle against the hand-derived golden vectors, and its Go-semantics helpers."""
+import random
+
+import pytest
+
+from oracle import ref_model as R
+from tests.helpers import oracle_for_case
+
+
+def test_oracle_matches_golden(golden_cases):
+    assert len(golden_cases) >= 40
+    for c in golden_cases:
+        src, plug = oracle_for_case(c)
+        for k, st in enumerate(c["steps"]):
+            before = len(src.patches)
+            envs = plug.Allocate(st["request"])
+            assert envs == st["expect_envs"], (c["name"], k)
+            if st["expect_patch"]:
+                ns, name, body = src.patches[before]
+                assert (ns, name) == (st["expect_patch"]["namespace"], st["expect_patch"]["name"])
+                assert body == st["expect_patch"]["body"].encode()
+            else:
+                assert len(src.patches) == before, (c["name"], k)
+
+
+def test_pattern_kat(oracle_lib, pattern_kat):
+    import ctypes
+    for v in pattern_kat:
+        w = (ctypes.c_uint32 * 4)()
+        oracle_lib.gs_oracle_pattern_word(ctypes.c_uint64(v["i"]), ctypes.c_uint32(v["seed"]), w)
+        assert list(w) == v["words"]
+    # first vector by hand: i = 0, seed = 0 => h = 0 through the whole mix
+    assert pattern_kat[0]["words"] == [0, 0xFFFFFFFF, 0, 0xC2B2AE3D]
+
+
+def test_oracle_pattern_check_counts(oracle_lib):
+    import ctypes
+    n = 1024
+    buf = (ctypes.c_uint32 * (4 * n))()
+    oracle_lib.gs_oracle_pattern_fill(buf, ctypes.c_uint64(10), ctypes.c_uint64(n), ctypes.c_uint32(3))
+    buf[4 * 100 + 2] ^= 0x00FF0000
+    buf[4 * 7 + 1] ^= 0x1
+    mm, fb, fl = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+    oracle_lib.gs_oracle_pattern_check(buf, ctypes.c_uint64(10), ctypes.c_uint64(n), ctypes.c_uint32(3),
+                                       ctypes.byref(mm), ctypes.byref(fb), ctypes.byref(fl))
+    assert (mm.value, fb.value, fl.value) == (2, (10 + 7) * 16 + 4, 9)
+
+
+@pytest.mark.parametrize("s,want", [("0", 0), ("-0", 0), ("+3", 3), ("007", 7), ("-12", -12),
+                                    ("9223372036854775807", 2**63 - 1),
+                                    ("-9223372036854775808", -2**63)])
+def test_go_atoi_ok(s, want):
+    assert R.go_atoi(s) == want
+
+
+@pytest.mark.parametrize("s", ["", "+", "-", " 1", "1 ", "1_0", "0x1", "1.0", "٣",
+                               "9223372036854775808", "-9223372036854775809", "++1"])
+def test_go_atoi_err(s):
+    with pytest.raises(ValueError):
+        R.go_atoi(s)
+
+
+def test_go_parse_uint():
+    assert R.go_parse_uint("18446744073709551615") == 2**64 - 1
+    for bad in ["", "+1", "-1", "18446744073709551616", "1e3", " 1"]:
+        with pytest.raises(ValueError):
+            R.go_parse_uint(bad)
+
+
+@pytest.mark.parametrize("s,want", [("2", 2), (2, 2), ("2000m", 2), ("1500m", 2), ("1m", 1),
+                                    ("0", 0), ("1Ki", 1024), ("1.5Gi", 1610612736),
+                                    ("2e3", 2000), ("2E3", 2000), ("1E", 10**18),
+                                    ("100n", 1), ("-1500m", -2), ("0.5", 1), ("12e-1", 2),
+                                    (".5", 1), ("5.", 5)])
+def test_quantity_value(s, want):
+    assert R.quantity_value(s) == want
+
+
+@pytest.mark.parametrize("s", ["", "abc", "1K", "1ki", "1 Gi", "1e", "e3", "--1", "1Gii"])
+def test_quantity_value_err(s):
+    with pytest.raises(ValueError):
+        R.quantity_value(s)
+
+
+def test_go_sort_small_is_insertion_with_reversed_ties():
+    keys = [5, 3, 5, 3, 1, 5]
+    idx = list(range(len(keys)))
+    R.go_sort_less_swap(len(idx), lambda i, j: keys[idx[i]] <= keys[idx[j]],
+                        lambda i, j: idx.__setitem__(slice(None), _swapped(idx, i, j)))
+    assert [(keys[k], k) for k in idx] == [(1, 4), (3, 3), (3, 1), (5, 5), (5, 2), (5, 0)]
+
+
+def _swapped(lst, i, j):
+    out = list(lst)
+    out[i], out[j] = out[j], out[i]
+    return out
+
+
+def test_go_sort_large_distinct_sorts():
+    rng = random.Random(20261106)
+    for n in (13, 14, 50, 64, 200, 1000):
+        for shape in ("random", "ascending", "descending", "organ"):
+            keys = rng.sample(range(10 * n), n)
+            if shape == "ascending":
+                keys.sort()
+            elif shape == "descending":
+                keys.sort(reverse=True)
+            elif shape == "organ":
+                keys.sort()
+                keys = keys[::2] + keys[1::2][::-1]
+            a = list(keys)
+
+            def swap(i, j):
+                a[i], a[j] = a[j], a[i]
+            R.go_sort_less_swap(n, lambda i, j: a[i] <= a[j], swap)
+            assert a == sorted(keys), (n, shape)
+
+
+def test_wire_roundtrip():
+    reqs = [["a-_-1", "b-_-22"], [], ["c" * 200]]
+    assert R.decode_allocate_request(R.encode_allocate_request(reqs)) == reqs
+    devs = [("GPU-x-_-0", "Healthy"), ("GPU-x-_-1", "Unhealthy")]
+    assert R.decode_list_and_watch(R.encode_list_and_watch(devs)) == devs
+
+
+def test_get_devices_order_and_h7():
+    g = R.Globals("GiB")
+    devs, names = R.getDevices(g, [("GPU-a", 16500), ("GPU-b", 81920)])
+    assert g.gpuMemory == 16 and len(devs) == 32
+    assert devs[0] == ["GPU-a-_-0", "Healthy"] and devs[16] == ["GPU-b-_-0", "Healthy"]
+    assert names == {"GPU-a": 0, "GPU-b": 1}
+    # H7: the global survives a "restart" with different hardware
+    devs2, _ = R.getDevices(g, [("GPU-c", 81920)])
+    assert len(devs2) == 16
+
+
+def test_watch_xids_rule():
+    g = R.Globals("GiB")
+    devs, _ = R.getDevices(g, [("GPU-a", 2048), ("GPU-b", 2048)])
+    assert R.watchXIDs_event(devs, "GPU-b", 79) == [2, 3]
+    assert R.watchXIDs_event(devs, "GPU-b", 31) == []
+    assert R.watchXIDs_event(devs, "GPU-b", 43) == []
+    assert R.watchXIDs_event(devs, "GPU-b", 45) == []
+    assert R.watchXIDs_event(devs, "", 79) == [0, 1, 2, 3]
+    assert R.watchXIDs_event(devs, None, 48) == [0, 1, 2, 3]

@@ -25,6 +25,20 @@ def main():
         sl = [(d, nbytes, 1234)]
         p.run(sl)  # warm
         forms_w, forms_v = range(4), range(5)
+        for code in [100 + 10 * st + sub for st in (0, 1) for sub in range(5)]:
+            p.set_variant(write=code)
+            ts = []
+            for _ in range(reps):
+                _, tm = p.run(sl, L.GS_PROBE_WRITE)
+                ts.append(tm.write_ms)
+            v, _ = p.run(sl, L.GS_PROBE_VERIFY)
+            assert v[0].clean, (code, v)
+            rec = dict(kind="write", code=code, ctas=1, best_gbps=nbytes / min(ts) / 1e6,
+                       med_gbps=nbytes / statistics.median(ts) / 1e6)
+            out.append(rec)
+            print(json.dumps(rec), flush=True)
+        if os.environ.get("SWEEP_BULK_ONLY"):
+            forms_w, forms_v = [], []
         for usel in (0, 1, 2):
             for ctas in (0, 2, 4, 8):
                 for fw in forms_w:
