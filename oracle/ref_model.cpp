@@ -1,0 +1,610 @@
+// oracle/ref_model.cpp -- cost-faithful C++ restatement of the reference's hot path.
+//
+// TEST INFRASTRUCTURE / CPU BASELINE ONLY: used by tests/ (cross-check against
+// oracle/ref_model.py and the product) and by bench.py's cpu_baseline leg and
+// `--impl reference` arm. The product never links or calls this file.
+//
+// PARITY UNPINNED: the reference is Go and cannot be built on either machine (no
+// toolchain, ~50 un-vendored modules), and its only test asserts nothing; there is
+// nothing of the reference's to pin this against (see oracle/ref_model.py header).
+//
+// Purpose: stand in for "the reference Go plugin timed on the box" (BASELINE.md
+// section 3). It does, per unit of work, what the Go code does -- not what a tuned
+// implementation would do:
+//   - request decode materialises one heap string per device id, as gogo's
+//     Unmarshal does for `repeated string devices_ids`, even though Allocate only
+//     takes len() of them (allocate.go:55-57);
+//   - getDevices formats "%s-_-%d" and heap-allocates a Device per memory unit
+//     (nvidia.go:70-82); every ListAndWatch send re-marshals the whole list
+//     (server.go:181,190), size pass + write pass like gogo;
+//   - pods are copied out of the lister's list, de-duplicated through a hash map
+//     keyed by UID, filtered, copied again (`current := pod` escapes to the heap,
+//     podmanager.go:306-309) and sorted with a comparator that looks the annotation
+//     up and parses it on every comparison (podmanager.go:340-343);
+//   - envs are built into a map with formatted values (allocate.go:116-124) and
+//     marshalled from it; the patch body goes through a nested map (podutils.go:27-35);
+//   - the whole Allocate runs under one mutex (allocate.go:60-61).
+// What it leaves out makes it FASTER than the Go original, so the baseline is
+// conservative: no glog calls (the reference logs ~8 lines per Allocate plus one per
+// pod, podmanager.go:281), no garbage collector, no gRPC/HTTP2 framing, no JSON decode
+// of the pod list (network I/O is replaced by the same in-memory pod source on both
+// arms).
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace {
+
+const char kResourceName[] = "aliyun.com/gpu-mem";          // const.go:11
+const char kEnvNVGPU[] = "NVIDIA_VISIBLE_DEVICES";           // const.go:24
+const char kEnvIdx[] = "ALIYUN_COM_GPU_MEM_IDX";             // const.go:25
+const char kEnvPod[] = "ALIYUN_COM_GPU_MEM_POD";             // const.go:26
+const char kEnvContainer[] = "ALIYUN_COM_GPU_MEM_CONTAINER"; // const.go:27
+const char kEnvDev[] = "ALIYUN_COM_GPU_MEM_DEV";             // const.go:28
+const char kEnvAssigned[] = "ALIYUN_COM_GPU_MEM_ASSIGNED";   // const.go:29
+const char kEnvAssumeTime[] = "ALIYUN_COM_GPU_MEM_ASSUME_TIME"; // const.go:30
+
+using StrMap = std::map<std::string, std::string>;
+
+// resource.Quantity after parsing: value = mant * 10^exp10 * 2^exp2 (sign in mant)
+struct Quantity {
+  __int128 mant = 0;
+  int exp10 = 0, exp2 = 0;
+  bool ok = false;
+  int64_t Value() const {  // rounds away from zero
+    __int128 v = mant < 0 ? -mant : mant;
+    int e = exp10;
+    for (; e > 0; --e) v *= 10;
+    v <<= exp2;
+    bool inexact = false;
+    for (; e < 0 && v != 0; ++e) {
+      if (v % 10) inexact = true;
+      v /= 10;
+    }
+    if (inexact) v += 1;
+    return (int64_t)(mant < 0 ? -v : v);
+  }
+};
+
+Quantity parse_quantity(const std::string &s) {
+  Quantity q;
+  size_t i = 0;
+  bool neg = false;
+  if (i < s.size() && (s[i] == '+' || s[i] == '-')) neg = s[i++] == '-';
+  int digits = 0;
+  for (; i < s.size() && s[i] >= '0' && s[i] <= '9'; ++i, ++digits) q.mant = q.mant * 10 + (s[i] - '0');
+  if (i < s.size() && s[i] == '.') {
+    for (++i; i < s.size() && s[i] >= '0' && s[i] <= '9'; ++i, ++digits) {
+      q.mant = q.mant * 10 + (s[i] - '0');
+      --q.exp10;
+    }
+  }
+  if (!digits) return q;
+  const std::string suf = s.substr(i);
+  static const std::map<std::string, int> dec = {{"n", -9}, {"u", -6}, {"m", -3}, {"", 0}, {"k", 3},
+                                                 {"M", 6},  {"G", 9},  {"T", 12}, {"P", 15}, {"E", 18}};
+  static const std::map<std::string, int> bin = {{"Ki", 10}, {"Mi", 20}, {"Gi", 30},
+                                                 {"Ti", 40}, {"Pi", 50}, {"Ei", 60}};
+  if (dec.count(suf)) q.exp10 += dec.at(suf);
+  else if (bin.count(suf)) q.exp2 = bin.at(suf);
+  else if (suf.size() > 1 && (suf[0] == 'e' || suf[0] == 'E')) {
+    size_t k = 1;
+    int sign = 1;
+    if (suf[k] == '+' || suf[k] == '-') sign = suf[k++] == '-' ? -1 : 1;
+    if (k >= suf.size()) return q;
+    int e = 0;
+    for (; k < suf.size(); ++k) {
+      if (suf[k] < '0' || suf[k] > '9') return q;
+      e = e * 10 + (suf[k] - '0');
+    }
+    q.exp10 += sign * e;
+  } else return q;
+  if (neg) q.mant = -q.mant;
+  q.ok = true;
+  return q;
+}
+
+struct Container {
+  std::map<std::string, Quantity> limits;
+};
+
+// Heap part of a v1.Pod that Go shares between struct copies (maps, slices, strings).
+struct PodData {
+  std::string uid, ns, name, node;
+  StrMap annotations;
+  std::vector<Container> containers;
+};
+
+// A v1.Pod VALUE: Go copies the struct (well over a kilobyte of headers: ObjectMeta,
+// PodSpec, PodStatus) while sharing what it points to.
+struct Pod {
+  std::shared_ptr<PodData> d;
+  char headers[1024];
+};
+
+struct Device {
+  std::string ID, Health;
+};
+
+bool parse_uint(const std::string &s, uint64_t *out) {  // strconv.ParseUint(s, 10, 64)
+  if (s.empty()) return false;
+  uint64_t v = 0;
+  for (char c : s) {
+    if (c < '0' || c > '9') return false;
+    const unsigned d = (unsigned)(c - '0');
+    if (v > (UINT64_MAX - d) / 10) return false;
+    v = v * 10 + d;
+  }
+  *out = v;
+  return true;
+}
+
+bool atoi_go(const std::string &s, int64_t *out) {  // strconv.Atoi
+  if (s.empty()) return false;
+  bool neg = false;
+  std::string body = s;
+  if (s[0] == '+' || s[0] == '-') {
+    neg = s[0] == '-';
+    body = s.substr(1);
+  }
+  uint64_t u;
+  if (!parse_uint(body, &u)) return false;
+  if (!neg && u > (uint64_t)INT64_MAX) return false;
+  if (neg && u > (uint64_t)INT64_MAX + 1) return false;
+  *out = neg ? (int64_t)(0 - u) : (int64_t)u;
+  return true;
+}
+
+uint64_t getAssumeTimeFromPodAnnotation(const Pod &pod) {  // podutils.go:64-75
+  uint64_t t = 0;
+  auto it = pod.d->annotations.find(kEnvAssumeTime);
+  if (it != pod.d->annotations.end()) {
+    uint64_t u;
+    if (parse_uint(it->second, &u)) t = u;
+  }
+  return t;
+}
+
+uint64_t getGPUMemoryFromPodResource(const Pod &pod) {  // podutils.go:122-131
+  uint64_t total = 0;
+  for (const Container &c : pod.d->containers) {
+    auto it = c.limits.find(kResourceName);
+    if (it != c.limits.end()) total += (uint64_t)it->second.Value();
+  }
+  return total;
+}
+
+bool isGPUMemoryAssumedPod(const Pod &pod) {  // podutils.go:78-119
+  if (getGPUMemoryFromPodResource(pod) <= 0) return false;
+  if (pod.d->annotations.find(kEnvAssumeTime) == pod.d->annotations.end()) return false;
+  auto it = pod.d->annotations.find(kEnvAssigned);
+  if (it != pod.d->annotations.end()) return it->second == "false";
+  return false;
+}
+
+int64_t getGPUIDFromPodAnnotation(const Pod &pod) {  // podutils.go:37-61
+  int64_t id = -1;
+  if (!pod.d->annotations.empty()) {
+    auto it = pod.d->annotations.find(kEnvIdx);
+    if (it != pod.d->annotations.end()) {
+      if (!atoi_go(it->second, &id)) id = -1;
+    }
+  }
+  return id;
+}
+
+// ---- protobuf, the way generated gogo code goes about it --------------------------
+const uint8_t *get_varint(const uint8_t *p, const uint8_t *end, uint64_t *out) {
+  uint64_t v = 0;
+  for (unsigned shift = 0; shift < 64; shift += 7) {
+    if (p >= end) return nullptr;
+    const uint8_t b = *p++;
+    v |= (uint64_t)(b & 0x7F) << shift;
+    if (!(b & 0x80)) {
+      *out = v;
+      return p;
+    }
+  }
+  return nullptr;
+}
+const uint8_t *skip_value(const uint8_t *p, const uint8_t *end, unsigned wt) {
+  uint64_t v;
+  if (wt == 0) return get_varint(p, end, &v);
+  if (wt == 1) return end - p >= 8 ? p + 8 : nullptr;
+  if (wt == 5) return end - p >= 4 ? p + 4 : nullptr;
+  if (wt == 2) {
+    p = get_varint(p, end, &v);
+    return (p && v <= (uint64_t)(end - p)) ? p + v : nullptr;
+  }
+  return nullptr;
+}
+size_t sov(uint64_t v) {
+  size_t n = 1;
+  while (v >= 0x80) {
+    v >>= 7;
+    ++n;
+  }
+  return n;
+}
+void put_varint(std::vector<uint8_t> &o, uint64_t v) {
+  while (v >= 0x80) {
+    o.push_back((uint8_t)(v | 0x80));
+    v >>= 7;
+  }
+  o.push_back((uint8_t)v);
+}
+void put_str_field(std::vector<uint8_t> &o, unsigned field, const std::string &s) {
+  put_varint(o, (field << 3) | 2);
+  put_varint(o, s.size());
+  o.insert(o.end(), s.begin(), s.end());
+}
+
+struct ContainerAllocateRequest {
+  std::vector<std::string> DevicesIDs;
+};
+struct AllocateRequest {
+  std::vector<std::unique_ptr<ContainerAllocateRequest>> ContainerRequests;
+};
+
+bool unmarshal_request(const uint8_t *buf, size_t len, AllocateRequest *req) {
+  const uint8_t *p = buf, *end = buf + len;
+  while (p < end) {
+    uint64_t key;
+    if (!(p = get_varint(p, end, &key))) return false;
+    if ((key >> 3) == 1 && (key & 7) == 2) {
+      uint64_t l;
+      if (!(p = get_varint(p, end, &l)) || l > (uint64_t)(end - p)) return false;
+      req->ContainerRequests.emplace_back(new ContainerAllocateRequest());
+      ContainerAllocateRequest *c = req->ContainerRequests.back().get();
+      const uint8_t *q = p, *qend = p + l;
+      while (q < qend) {
+        uint64_t k2;
+        if (!(q = get_varint(q, qend, &k2))) return false;
+        if ((k2 >> 3) == 1 && (k2 & 7) == 2) {
+          uint64_t sl;
+          if (!(q = get_varint(q, qend, &sl)) || sl > (uint64_t)(qend - q)) return false;
+          c->DevicesIDs.emplace_back((const char *)q, (size_t)sl);  // string(dAtA[i:j])
+          q += sl;
+        } else if (!(q = skip_value(q, qend, (unsigned)(k2 & 7)))) {
+          return false;
+        }
+      }
+      p = qend;
+    } else if (!(p = skip_value(p, end, (unsigned)(key & 7)))) {
+      return false;
+    }
+  }
+  return true;
+}
+
+using Envs = StrMap;  // map[string]string; marshalled in whatever order the map yields
+
+size_t envs_size(const Envs &e) {
+  size_t n = 0;
+  for (const auto &kv : e) {
+    const size_t entry = 1 + sov(kv.first.size()) + kv.first.size() + 1 + sov(kv.second.size()) +
+                         kv.second.size();
+    n += 1 + sov(entry) + entry;
+  }
+  return n;
+}
+
+void marshal_response(const std::vector<std::unique_ptr<Envs>> &responses, std::vector<uint8_t> &o) {
+  size_t total = 0;  // Size() pass, then the write pass
+  for (const auto &e : responses) {
+    const size_t n = envs_size(*e);
+    total += 1 + sov(n) + n;
+  }
+  o.clear();
+  o.reserve(total);
+  for (const auto &e : responses) {
+    put_varint(o, (1u << 3) | 2);
+    put_varint(o, envs_size(*e));
+    for (const auto &kv : *e) {
+      const size_t entry = 1 + sov(kv.first.size()) + kv.first.size() + 1 + sov(kv.second.size()) +
+                           kv.second.size();
+      put_varint(o, (1u << 3) | 2);
+      put_varint(o, entry);
+      put_str_field(o, 1, kv.first);
+      put_str_field(o, 2, kv.second);
+    }
+  }
+}
+
+std::string sprintf_u(const char *fmt, uint64_t v) {
+  char b[64];
+  snprintf(b, sizeof b, fmt, (unsigned long long)v);
+  return b;
+}
+
+}  // namespace
+
+// ---- NvidiaDevicePlugin (server.go:19-35) and package globals (nvidia.go:12-15) -----
+struct RefPlugin {
+  std::string metric;      // "GiB" / "MiB"
+  uint64_t gpuMemory = 0;  // set once from GPU 0 (nvidia.go:67-69)
+  std::vector<std::pair<std::string, uint64_t>> gpus;  // (uuid, MiB-valued raw total)
+  std::vector<std::unique_ptr<Device>> devs;
+  std::map<std::string, unsigned> devNameMap;
+  std::map<unsigned, std::string> devIndxMap;
+  std::string nodeName;
+  bool disableCGPUIsolation = false;
+  std::mutex mu;
+  std::vector<Pod> podList;  // what the lister returns (podmanager.go:187-245)
+  std::vector<uint8_t> scratch;
+  int last_patched = -1;
+  std::string last_patch;
+
+  void setGPUMemory(uint64_t raw) {  // nvidia.go:31-38
+    uint64_t v = raw;
+    if (metric == "GiB") v = raw / 1024;
+    gpuMemory = v;
+  }
+
+  void getDevices() {  // nvidia.go:50-86
+    devs.clear();
+    devNameMap.clear();
+    for (size_t i = 0; i < gpus.size(); ++i) {
+      devNameMap[gpus[i].first] = (unsigned)i;
+      if (gpuMemory == 0) setGPUMemory(gpus[i].second);
+      for (uint64_t j = 0; j < gpuMemory; ++j) {
+        char id[160];
+        snprintf(id, sizeof id, "%s-_-%llu", gpus[i].first.c_str(), (unsigned long long)j);
+        devs.emplace_back(new Device{id, "Healthy"});
+      }
+    }
+  }
+
+  bool GetDeviceNameByIndex(uint64_t index, std::string *name) {  // server.go:80-91
+    if (devIndxMap.empty())
+      for (const auto &kv : devNameMap) devIndxMap[kv.second] = kv.first;
+    auto it = devIndxMap.find((unsigned)index);
+    if (index > 0xFFFFFFFFull || it == devIndxMap.end()) return false;
+    *name = it->second;
+    return true;
+  }
+
+  // server.go:181,190 -- s.Send(&ListAndWatchResponse{Devices: m.devs})
+  void marshalListAndWatch(std::vector<uint8_t> &o) {
+    size_t total = 0;
+    for (const auto &d : devs) {
+      const size_t inner = 1 + sov(d->ID.size()) + d->ID.size() + 1 + sov(d->Health.size()) +
+                           d->Health.size();
+      total += 1 + sov(inner) + inner;
+    }
+    o.clear();
+    o.reserve(total);
+    for (const auto &d : devs) {
+      const size_t inner = 1 + sov(d->ID.size()) + d->ID.size() + 1 + sov(d->Health.size()) +
+                           d->Health.size();
+      put_varint(o, (1u << 3) | 2);
+      put_varint(o, inner);
+      put_str_field(o, 1, d->ID);
+      put_str_field(o, 2, d->Health);
+    }
+  }
+
+  // podmanager.go:247-297
+  std::vector<Pod> getPendingPodsInNode() {
+    std::vector<Pod> pods;
+    std::unordered_map<std::string, bool> podIDMap;
+    for (const Pod &pod : podList) {
+      if (pod.d->node != nodeName) continue;
+      if (podIDMap.find(pod.d->uid) == podIDMap.end()) {
+        pods.push_back(pod);
+        podIDMap[pod.d->uid] = true;
+      }
+    }
+    return pods;
+  }
+
+  // podmanager.go:300-347
+  std::vector<std::unique_ptr<Pod>> getCandidatePods() {
+    std::vector<std::unique_ptr<Pod>> candidatePods;
+    std::vector<Pod> allPods = getPendingPodsInNode();
+    for (const Pod &pod : allPods) {
+      std::unique_ptr<Pod> current(new Pod(pod));  // `current := pod` escapes
+      if (isGPUMemoryAssumedPod(*current)) candidatePods.push_back(std::move(current));
+    }
+    // makePodOrderdByAge: sort.Sort with Less = `<=`. n <= 12 is Go's insertion sort
+    // (ties reversed); above that std::sort on a strict key stands in for pdqsort --
+    // the benchmark workloads use distinct assume times, where every correct sort agrees.
+    const int n = (int)candidatePods.size();
+    if (n <= 12) {
+      for (int i = 1; i < n; ++i)
+        for (int j = i; j > 0 && getAssumeTimeFromPodAnnotation(*candidatePods[j]) <=
+                                     getAssumeTimeFromPodAnnotation(*candidatePods[j - 1]);
+             --j)
+          std::swap(candidatePods[j], candidatePods[j - 1]);
+    } else {
+      std::sort(candidatePods.begin(), candidatePods.end(),
+                [](const std::unique_ptr<Pod> &a, const std::unique_ptr<Pod> &b) {
+                  return getAssumeTimeFromPodAnnotation(*a) < getAssumeTimeFromPodAnnotation(*b);
+                });
+    }
+    return candidatePods;
+  }
+
+  void buildErrResponse(const AllocateRequest &reqs, uint64_t podReqGPU,
+                        std::vector<std::unique_ptr<Envs>> &responses) {  // allocate.go:25-40
+    responses.clear();
+    for (const auto &req : reqs.ContainerRequests) {
+      std::unique_ptr<Envs> e(new Envs());
+      char b[96];
+      snprintf(b, sizeof b, "no-gpu-has-%llu%s-to-run", (unsigned long long)podReqGPU, metric.c_str());
+      (*e)[kEnvNVGPU] = b;
+      (*e)[kEnvIdx] = "-1";
+      (*e)[kEnvPod] = sprintf_u("%llu", podReqGPU);
+      (*e)[kEnvContainer] = sprintf_u("%llu", req->DevicesIDs.size());
+      (*e)[kEnvDev] = sprintf_u("%llu", gpuMemory);
+      responses.push_back(std::move(e));
+    }
+  }
+
+  // allocate.go:43-201; kinds as in include/gpushare.h (0 matched, 1 single-gpu,
+  // 2 no match, 3 bad index)
+  int Allocate(const uint8_t *buf, size_t len, int64_t now, std::vector<uint8_t> &out) {
+    AllocateRequest reqs;
+    if (!unmarshal_request(buf, len, &reqs)) return -4;
+    std::vector<std::unique_ptr<Envs>> responses;
+    uint64_t podReqGPU = 0;
+    for (const auto &req : reqs.ContainerRequests) podReqGPU += req->DevicesIDs.size();
+    std::lock_guard<std::mutex> lk(mu);
+    last_patched = -1;
+    std::vector<std::unique_ptr<Pod>> pods = getCandidatePods();
+    Pod *assumePod = nullptr;
+    for (auto &pod : pods) {
+      if (getGPUMemoryFromPodResource(*pod) == podReqGPU) {
+        assumePod = pod.get();
+        break;
+      }
+    }
+    int kind;
+    if (assumePod) {
+      int64_t id = getGPUIDFromPodAnnotation(*assumePod);
+      std::string candidateDevID;
+      if (id >= 0 && !GetDeviceNameByIndex((uint64_t)id, &candidateDevID)) id = -1;
+      if (id < 0) {
+        buildErrResponse(reqs, podReqGPU, responses);
+        kind = 3;
+      } else {
+        for (const auto &req : reqs.ContainerRequests) {
+          std::unique_ptr<Envs> e(new Envs());
+          char b[32];
+          snprintf(b, sizeof b, "%lld", (long long)id);
+          (*e)[kEnvNVGPU] = b;
+          (*e)[kEnvIdx] = b;
+          (*e)[kEnvPod] = sprintf_u("%llu", podReqGPU);
+          (*e)[kEnvContainer] = sprintf_u("%llu", req->DevicesIDs.size());
+          (*e)[kEnvDev] = sprintf_u("%llu", gpuMemory);
+          if (disableCGPUIsolation) (*e)["CGPU_DISABLE"] = "true";
+          responses.push_back(std::move(e));
+        }
+        // patchPodAnnotationSpecAssigned (podutils.go:27-35) via nested maps
+        std::map<std::string, std::map<std::string, StrMap>> patch;
+        char t[32];
+        snprintf(t, sizeof t, "%lld", (long long)now);
+        patch["metadata"]["annotations"][kEnvAssigned] = "true";
+        patch["metadata"]["annotations"][kEnvAssumeTime] = t;
+        std::string body = "{";
+        for (const auto &a : patch) {
+          body += "\"" + a.first + "\":{";
+          for (const auto &b2 : a.second) {
+            body += "\"" + b2.first + "\":{";
+            bool first = true;
+            for (const auto &c : b2.second) {
+              if (!first) body += ",";
+              first = false;
+              body += "\"" + c.first + "\":\"" + c.second + "\"";
+            }
+            body += "}";
+          }
+          body += "}";
+        }
+        body += "}";
+        last_patch = body;
+        // the PATCH (allocate.go:136) lands in the in-memory pod source
+        for (size_t i = 0; i < podList.size(); ++i) {
+          if (podList[i].d->ns == assumePod->d->ns && podList[i].d->name == assumePod->d->name) {
+            podList[i].d->annotations[kEnvAssigned] = "true";
+            podList[i].d->annotations[kEnvAssumeTime] = t;
+            last_patched = (int)i;
+            break;
+          }
+        }
+        kind = 0;
+      }
+    } else if (devNameMap.size() == 1) {  // allocate.go:154-180
+      const auto &only = *devNameMap.begin();
+      for (const auto &req : reqs.ContainerRequests) {
+        std::unique_ptr<Envs> e(new Envs());
+        (*e)[kEnvNVGPU] = only.first;
+        (*e)[kEnvIdx] = sprintf_u("%llu", only.second);
+        (*e)[kEnvPod] = sprintf_u("%llu", podReqGPU);
+        (*e)[kEnvContainer] = sprintf_u("%llu", req->DevicesIDs.size());
+        (*e)[kEnvDev] = sprintf_u("%llu", gpuMemory);
+        if (disableCGPUIsolation) (*e)["CGPU_DISABLE"] = "true";
+        responses.push_back(std::move(e));
+      }
+      kind = 1;
+    } else {
+      buildErrResponse(reqs, podReqGPU, responses);
+      kind = 2;
+    }
+    marshal_response(responses, out);
+    return kind;
+  }
+};
+
+#define REF_EXPORT extern "C" __attribute__((visibility("default")))
+
+REF_EXPORT void *ref_new(const char *const *uuids, int n, uint64_t raw_mib, const char *metric,
+                         const char *node, int cgpu) {
+  RefPlugin *p = new RefPlugin();
+  p->metric = metric;
+  p->nodeName = node;
+  p->disableCGPUIsolation = cgpu != 0;
+  for (int i = 0; i < n; ++i) p->gpus.emplace_back(uuids[i], raw_mib);
+  p->getDevices();
+  return p;
+}
+REF_EXPORT void ref_free(void *h) { delete (RefPlugin *)h; }
+REF_EXPORT uint64_t ref_get_devices(void *h) {  // hot loop A again (plugin restart)
+  RefPlugin *p = (RefPlugin *)h;
+  p->getDevices();
+  return p->devs.size();
+}
+REF_EXPORT uint64_t ref_units(void *h) { return ((RefPlugin *)h)->gpuMemory; }
+REF_EXPORT void ref_clear_pods(void *h) { ((RefPlugin *)h)->podList.clear(); }
+// limits[i] == NULL: container i has no aliyun.com/gpu-mem limit
+REF_EXPORT void ref_add_pod(void *h, const char *uid, const char *ns, const char *name,
+                            const char *node, int n_containers, const char *const *limits,
+                            int n_ann, const char *const *keys, const char *const *vals) {
+  RefPlugin *p = (RefPlugin *)h;
+  Pod pod;
+  memset(pod.headers, 0, sizeof pod.headers);
+  pod.d = std::make_shared<PodData>();
+  pod.d->uid = uid;
+  pod.d->ns = ns;
+  pod.d->name = name;
+  pod.d->node = node;
+  for (int i = 0; i < n_containers; ++i) {
+    Container c;
+    if (limits[i]) c.limits[kResourceName] = parse_quantity(limits[i]);
+    pod.d->containers.push_back(c);
+  }
+  for (int i = 0; i < n_ann; ++i) pod.d->annotations[keys[i]] = vals[i];
+  p->podList.push_back(pod);
+}
+REF_EXPORT int ref_allocate(void *h, const uint8_t *req, size_t len, int64_t now, uint8_t *resp,
+                            size_t cap, size_t *resp_len) {
+  RefPlugin *p = (RefPlugin *)h;
+  const int kind = p->Allocate(req, len, now, p->scratch);
+  *resp_len = p->scratch.size();
+  if (p->scratch.size() <= cap && resp) memcpy(resp, p->scratch.data(), p->scratch.size());
+  return kind;
+}
+REF_EXPORT int ref_last_patched(void *h) { return ((RefPlugin *)h)->last_patched; }
+REF_EXPORT size_t ref_last_patch(void *h, char *buf, size_t cap) {
+  RefPlugin *p = (RefPlugin *)h;
+  if (p->last_patch.size() <= cap) memcpy(buf, p->last_patch.data(), p->last_patch.size());
+  return p->last_patch.size();
+}
+REF_EXPORT size_t ref_list_and_watch(void *h, uint8_t *buf, size_t cap) {
+  RefPlugin *p = (RefPlugin *)h;
+  p->marshalListAndWatch(p->scratch);
+  if (buf && p->scratch.size() <= cap) memcpy(buf, p->scratch.data(), p->scratch.size());
+  return p->scratch.size();
+}
+REF_EXPORT void ref_mark_unhealthy(void *h, uint64_t dev_index) {  // server.go:189
+  RefPlugin *p = (RefPlugin *)h;
+  if (dev_index < p->devs.size()) p->devs[dev_index]->Health = "Unhealthy";
+}

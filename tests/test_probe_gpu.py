@@ -1,0 +1,170 @@
+"""Slice probe (K1) on a real GPU, through the C ABI, against the CPU pattern oracle."""
+import ctypes
+
+import pytest
+
+from gpushare_b200 import _lib as L
+
+pytestmark = pytest.mark.gpu
+
+MiB = 1 << 20
+
+
+@pytest.fixture(scope="module")
+def probe():
+    from gpushare_b200.probe import Probe
+    p = Probe(0)
+    yield p
+    p.close()
+
+
+def oracle_bytes(oracle_lib, nbytes, seed, first=0):
+    buf = (ctypes.c_uint32 * (nbytes // 4))()
+    oracle_lib.gs_oracle_pattern_fill(buf, ctypes.c_uint64(first), ctypes.c_uint64(nbytes // 16),
+                                      ctypes.c_uint32(seed))
+    return bytes(buf)
+
+
+@pytest.mark.parametrize("nbytes", [16, 4096, 64 * 1024, 64 * 1024 + 16, MiB - 16, 3 * MiB + 4080,
+                                    37 * MiB])
+@pytest.mark.parametrize("wvariant", [102, 100, 110, 0, 21])
+def test_written_pattern_is_bit_exact(probe, oracle_lib, nbytes, wvariant):
+    d = probe.alloc(nbytes + 256)
+    try:
+        probe.set_variant(write=wvariant)
+        v, tm = probe.run([(d, nbytes, 0xC0FFEE)])
+        assert v[0].clean and tm.launches == 2 and tm.bytes == nbytes
+        assert probe.read(d, nbytes) == oracle_bytes(oracle_lib, nbytes, 0xC0FFEE)
+    finally:
+        probe.set_variant(write=102)
+        probe.free(d)
+
+
+@pytest.mark.parametrize("vvariant", [0, 1, 2, 3, 4, 10, 21])
+def test_verify_counts_match_oracle(probe, oracle_lib, vvariant):
+    nbytes = 5 * MiB + 48
+    d = probe.alloc(nbytes)
+    try:
+        probe.set_variant(verify=vvariant)
+        probe.run([(d, nbytes, 9)], L.GS_PROBE_WRITE)
+        host = bytearray(oracle_bytes(oracle_lib, nbytes, 9))
+        for off, mask in [(0, 0x1), (4 * 1000, 0x00010100), (64 * 1024 - 4, 0xFFFFFFFF),
+                          (64 * 1024, 0x80000000), (nbytes - 4, 0x3), (nbytes - 16, 0x40),
+                          (2 * MiB + 8, 0x8000)]:
+            probe.inject(d, off, mask)
+            word = int.from_bytes(host[off:off + 4], "little") ^ mask
+            host[off:off + 4] = word.to_bytes(4, "little")
+        assert probe.read(d, nbytes) == bytes(host)
+        mm, fb, fl = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+        arr = (ctypes.c_uint32 * (nbytes // 4)).from_buffer(host)
+        oracle_lib.gs_oracle_pattern_check(arr, ctypes.c_uint64(0), ctypes.c_uint64(nbytes // 16),
+                                           ctypes.c_uint32(9), ctypes.byref(mm), ctypes.byref(fb),
+                                           ctypes.byref(fl))
+        v, _ = probe.run([(d, nbytes, 9)], L.GS_PROBE_VERIFY)
+        assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == (mm.value, fb.value, fl.value)
+        assert mm.value == 6 and fb.value == 0
+    finally:
+        probe.set_variant(verify=0)
+        probe.free(d)
+
+
+def test_wrong_seed_is_all_mismatch(probe):
+    nbytes = 2 * MiB
+    d = probe.alloc(nbytes)
+    try:
+        probe.run([(d, nbytes, 1)], L.GS_PROBE_WRITE)
+        v, _ = probe.run([(d, nbytes, 2)], L.GS_PROBE_VERIFY)
+        assert v[0].mismatches == nbytes // 16 and v[0].first_bad_byte == 0
+    finally:
+        probe.free(d)
+
+
+def test_batch_of_tenant_slices_is_independent(probe, oracle_lib):
+    """BASELINE config 4 shape in miniature: many slices, one launch pair, per-slice verdicts."""
+    sizes = [MiB, 3 * MiB + 16, 64 * 1024, 17 * MiB, 16, 5 * MiB, 2 * MiB + 4096, 9 * MiB]
+    arena = probe.alloc(sum(sizes))
+    try:
+        slices, off = [], 0
+        for k, n in enumerate(sizes):
+            slices.append((arena + off, n, 100 + k, k))
+            off += n
+        v, tm = probe.run(slices)
+        assert all(x.clean for x in v) and tm.launches == 2 and tm.bytes == sum(sizes)
+        for (base, n, seed, _k) in slices:
+            assert probe.read(base, n) == oracle_bytes(oracle_lib, n, seed)
+        probe.inject(slices[3][0], 4 * MiB, 0xF0)       # inside slice 3 only
+        probe.inject(slices[6][0], 0, 0x1)              # first word of slice 6
+        v, _ = probe.run(slices, L.GS_PROBE_VERIFY)
+        assert [x.mismatches for x in v] == [0, 0, 0, 1, 0, 0, 1, 0]
+        assert v[3].first_bad_byte == 4 * MiB and v[3].bit_flips == 4
+        assert v[6].first_bad_byte == 0 and v[6].bit_flips == 1
+    finally:
+        probe.free(arena)
+
+
+def test_max_slices_and_argument_errors(probe):
+    arena = probe.alloc(65 * 4096)
+    try:
+        sl = [(arena + 4096 * k, 4096, k) for k in range(65)]
+        v, _ = probe.run(sl[:64])
+        assert len(v) == 64 and all(x.clean for x in v)
+        for bad, status in [(sl, L.GS_E_LIMIT), ([(arena + 8, 4096, 0)], L.GS_E_INVAL),
+                            ([(arena, 24, 0)], L.GS_E_INVAL), ([(arena, 0, 0)], L.GS_E_INVAL),
+                            ([(0, 4096, 0)], L.GS_E_INVAL)]:
+            with pytest.raises(L.GpushareError) as e:
+                probe.run(bad)
+            assert e.value.status == status
+        probe.submit(sl[:2])
+        with pytest.raises(L.GpushareError) as e:
+            probe.submit(sl[:2])                         # one batch in flight at a time
+        assert e.value.status == L.GS_E_STATE
+        probe.wait()
+    finally:
+        probe.free(arena)
+
+
+def test_word_index_above_2_to_32(probe, oracle_lib):
+    """Slices beyond 64 GiB carry a non-zero high index word; check the tail of a 65 GiB slice
+    (whole-GPU health probes reach this). Skipped when the GPU lacks the room."""
+    nbytes = 65 << 30
+    free, _total = probe.mem_info()
+    if free < nbytes + (1 << 30):
+        pytest.skip("not enough free HBM")
+    d = probe.alloc(nbytes)
+    try:
+        v, tm = probe.run([(d, nbytes, 31337)])
+        assert v[0].clean
+        tail = 4 * MiB
+        first = (nbytes - tail) // 16
+        assert first > 1 << 32
+        assert probe.read(d + nbytes - tail, tail) == oracle_bytes(oracle_lib, tail, 31337, first)
+        probe.inject(d, nbytes - 8, 0x2)
+        v, _ = probe.run([(d, nbytes, 31337)], L.GS_PROBE_VERIFY)
+        assert (v[0].mismatches, v[0].first_bad_byte) == (1, nbytes - 8)
+    finally:
+        probe.free(d)
+
+
+def test_run_granted_and_round_trip_property(probe):
+    """Full-size property (no oracle needed): write -> verify is clean for any seed, and a
+    verify with any other seed reports every word."""
+    from gpushare_b200.probe import run_granted
+    v, tm = run_granted(0, 2 << 30, 77)
+    assert v.clean and tm.bytes == 2 << 30 and tm.gbps() > 1000
+
+
+def test_nvml_enumeration_and_ordinal_map():
+    from gpushare_b200 import api
+    with api.Nvml() as nv:
+        infos = nv.devices()
+        assert len(infos) >= 1 and infos[0].uuid.startswith(b"GPU-")
+        assert infos[0].total_bytes >> 20 > 150000     # B200: 183 359 MiB
+        ords = nv.map_cuda_ordinals(infos)
+        assert sorted(o for o in ords if o >= 0) == list(range(len([o for o in ords if o >= 0])))
+        t = api.DeviceTable.from_gpus(infos, "GiB")
+        assert t.units_per_gpu == (infos[0].total_bytes >> 20) // 1024
+
+
+def test_smoke_entry():
+    import __graft_entry__
+    __graft_entry__.smoke()
