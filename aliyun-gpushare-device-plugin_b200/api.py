@@ -10,6 +10,7 @@ Everything here forwards to libgpushare_core.so; there is no Python implementati
 any decision, encoding or probe.
 """
 import ctypes as C
+import threading
 from dataclasses import dataclass
 
 from . import _lib as L
@@ -308,6 +309,14 @@ def pod_views(pods):
     return arr, keep
 
 
+class PodList:
+    """Pods already laid out as the C ABI's gs_pod_view array (what a lister hands over)."""
+
+    def __init__(self, pods):
+        self.n = len(pods)
+        self.views, self._keep = pod_views(pods)
+
+
 @dataclass
 class AllocDecision:
     kind: str
@@ -380,7 +389,7 @@ class NvidiaDevicePlugin:
         L.check(self.lib.gs_plugin_new(table.h, b, len(b), int(disable_cgpu_isolation),
                                        C.byref(h)), "gs_plugin_new")
         self.h = h
-        self._resp = C.create_string_buffer(1 << 16)
+        self._tls = threading.local()   # one response buffer per calling thread
 
     def close(self):
         if self.h:
@@ -394,8 +403,11 @@ class NvidiaDevicePlugin:
             pass
 
     def set_pods(self, pods):
-        views, keep = pod_views(pods)
-        L.check(self.lib.gs_plugin_set_pods(self.h, views, len(pods)), "gs_plugin_set_pods")
+        """Replace the pod source. `pods` is a list of Pod, or a PodList prepared once with
+        PodList(pods) when the same list is installed repeatedly."""
+        if not isinstance(pods, PodList):
+            pods = PodList(pods)
+        L.check(self.lib.gs_plugin_set_pods(self.h, pods.views, pods.n), "gs_plugin_set_pods")
 
     def set_clock(self, fixed_unix_nano):
         L.check(self.lib.gs_plugin_set_clock(self.h, fixed_unix_nano))
@@ -418,10 +430,13 @@ class NvidiaDevicePlugin:
     # --- the five RPC bodies, bytes in / bytes out ---------------------------------
     def Allocate(self, request: bytes) -> AllocDecision:
         res = L.AllocResult()
-        rc = self.lib.gs_plugin_allocate(self.h, request, len(request), self._resp,
-                                         len(self._resp), C.byref(res))
+        buf = getattr(self._tls, "resp", None)
+        if buf is None:
+            buf = self._tls.resp = C.create_string_buffer(1 << 16)
+        rc = self.lib.gs_plugin_allocate(self.h, request, len(request), buf, len(buf),
+                                         C.byref(res))
         L.check(rc, "gs_plugin_allocate")
-        return _decision(res, self._resp.raw[:res.resp_len])
+        return _decision(res, C.string_at(buf, res.resp_len))
 
     def GetDevicePluginOptions(self, request: bytes = b"") -> bytes:
         n = C.c_size_t()

@@ -126,3 +126,77 @@ def run_granted(cuda_ordinal, nbytes, seed):
             "gs_probe_run_granted")
     return (SliceVerdict(res.mismatches, res.first_bad_byte, res.bit_flips),
             Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches))
+
+
+class ProbeScheduler:
+    """Runs slice probes beside Allocate without ever making Allocate wait.
+
+    Allocate's answer never depends on the probe (bit-exact parity with the reference,
+    which has no probe), so grants are queued here and sent to the GPU whenever the
+    engine is idle: one batch (<= GS_PROBE_MAX_SLICES slices) in flight per GPU. When
+    grants arrive faster than HBM can be swept, the newest grants win and the dropped
+    ones are counted -- coverage is reported, never faked. A verdict with mismatches is
+    handed to `on_bad(tag, verdict)` (the daemon marks the GPU unhealthy there).
+    """
+
+    def __init__(self, probe: Probe, on_bad=None, max_pending=L.GS_PROBE_MAX_SLICES):
+        self.probe = probe
+        self.on_bad = on_bad
+        self.max_pending = max_pending
+        self.pending = []
+        self.inflight = None
+        self.batches = 0
+        self.launches = 0
+        self.bytes_probed = 0
+        self.bytes_granted = 0
+        self.dropped = 0
+        self.coalesced = 0
+        self.write_ms = 0.0
+        self.verify_ms = 0.0
+        self.bad = 0
+
+    def grant(self, base, nbytes, seed, tag=0):
+        self.bytes_granted += nbytes
+        for i, g in enumerate(self.pending):
+            if g[0] == base:                      # same range granted again before it was
+                self.pending[i] = (base, nbytes, seed, tag)   # swept: one sweep covers both
+                self.coalesced += 1
+                return
+        if len(self.pending) >= self.max_pending:
+            self.pending.pop(0)
+            self.dropped += 1
+        self.pending.append((base, nbytes, seed, tag))
+
+    def _collect(self):
+        verdicts, tm = self.probe.wait()
+        self.batches += 1
+        self.launches += tm.launches
+        self.bytes_probed += tm.bytes
+        self.write_ms += tm.write_ms
+        self.verify_ms += tm.verify_ms
+        for s, v in zip(self.inflight, verdicts):
+            if not v.clean:
+                self.bad += 1
+                if self.on_bad:
+                    self.on_bad(s[3], v)
+        self.inflight = None
+
+    def pump(self):
+        """Non-blocking: harvest a finished batch, start the next one."""
+        if self.inflight is not None and self.probe.idle():
+            self._collect()
+        if self.inflight is None and self.pending:
+            batch, self.pending = self.pending, []
+            self.probe.submit(batch)
+            self.inflight = batch
+
+    def drain(self):
+        """Blocking: finish what is in flight and what is queued."""
+        while self.inflight is not None or self.pending:
+            if self.inflight is not None:
+                self._collect()
+            self.pump()
+
+    def gbps(self):
+        t = self.write_ms + self.verify_ms
+        return 2 * self.bytes_probed / (t * 1e-3) / 1e9 if t > 0 else 0.0
