@@ -52,6 +52,8 @@ def tenant_sizes_gib(rank):
     one B200 (sum <= 160 GiB so the probed ranges fit beside the CUDA context)."""
     import random
     rng = random.Random(SEED + rank)
+    if os.environ.get("GS_BENCH_SMALL"):               # CPU tests: MiB-sized tenants
+        return rng.sample(range(1, 40), TENANTS)
     while True:
         s = [rng.randint(1, 40) for _ in range(TENANTS)]
         if len(set(s)) == TENANTS and sum(s) <= 160:   # distinct sizes: the size picks the pod
@@ -63,11 +65,12 @@ def build_workload(rank, uuid, units):
     import numpy as np
     from oracle import ref_model as R
     sizes = tenant_sizes_gib(rank)
+    per = 16 if os.environ.get("GS_BENCH_SMALL") else 1024   # units per size step
     rng = np.random.default_rng(SEED + 1000 * rank)
     free = rng.permutation(units)                      # ids drawn without replacement
     wires, off = [], 0
     for gib in sizes:
-        n = gib * 1024
+        n = gib * per
         ids = ["%s-_-%d" % (uuid, j) for j in free[off:off + n]]
         off += n
         wires.append(R.encode_allocate_request([ids]))
@@ -79,7 +82,7 @@ def build_workload(rank, uuid, units):
                                                   "ALIYUN_COM_GPU_MEM_ASSUME_TIME": str(10**18 + 977 * k),
                                                   "ALIYUN_COM_GPU_MEM_ASSIGNED": "false"}},
                      "spec": {"nodeName": NODE, "containers": [
-                         {"name": "main", "resources": {"limits": {"aliyun.com/gpu-mem": str(gib * 1024)}}}]},
+                         {"name": "main", "resources": {"limits": {"aliyun.com/gpu-mem": str(gib * per)}}}]},
                      "status": {"phase": "Pending"}})
     for k in range(PODS_IN_LIST - TENANTS):
         pods.append({"metadata": {"uid": "bg-%d-%d" % (rank, k), "name": "running-%d" % k,
