@@ -150,6 +150,7 @@ SIGNATURES = {
     "gs_probe_read": (_int, [_vp, _vp, _vp, _u64]),
     "gs_probe_set_variant": (_int, [_vp, _int, _int, _int]),
     "gs_probe_set_write_rate": (_int, [_vp, _u32]),
+    "gs_probe_verify_noalloc": (_int, [_int, _vp, _P(Slice), _u32, _P(SliceResult)]),
 }
 
 _lib = None

@@ -21,6 +21,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "gpushare.h"
 #include "internal.h"
 
@@ -678,3 +680,93 @@ int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t bytes) {
 }
 
 }  // extern "C"
+
+// ---- read-back pass for callers that may not allocate -----------------------------
+// Who cannot allocate: the plugin's health checker on a GPU whose HBM has been handed
+// out to tenants down to the last unit (a cudaMalloc there either fails or takes memory
+// a tenant was promised), and any caller on a path where cudaMalloc/cudaFree's implicit
+// device-wide synchronisation would stall the tenants' own kernels. For them the
+// per-slice verdict table -- the only global memory the load+compare kernel needs besides
+// the slices themselves -- lives in the fixed array below instead of a cudaMalloc'ed one.
+// Every GPU that loads this library carries the array (2 KiB) until the process exits.
+namespace {
+
+constexpr uint32_t kNoAllocMaxSlices = GS_PROBE_NOALLOC_MAX_SLICES;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) DevResult g_noalloc_verdicts[kNoAllocMaxSlices];
+
+// In host code `g_noalloc_verdicts` is only a handle for the runtime, not a device
+// address; the address a kernel can use is looked up once per device and kept here.
+DevResult *g_noalloc_ptr[kNoAllocMaxDevices];
+int g_noalloc_sms[kNoAllocMaxDevices];
+std::mutex g_noalloc_mu;
+
+}  // namespace
+
+extern "C" int gs_probe_verify_noalloc(int cuda_ordinal, void *stream, const gs_slice *slices,
+                                       uint32_t n, gs_slice_result *results) {
+  if (cuda_ordinal < 0 || cuda_ordinal >= kNoAllocMaxDevices || !slices || !results || n == 0)
+    return GS_E_INVAL;
+  if (n > kNoAllocMaxSlices) {
+    gs_internal::set_cuda_error("gs_probe_verify_noalloc", 0,
+                                "more slices than the fixed verdict table holds "
+                                "(GS_PROBE_NOALLOC_MAX_SLICES)");
+    return GS_E_LIMIT;
+  }
+  Batch b;
+  memset(&b, 0, sizeof(b));
+  uint64_t tiles = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const gs_slice &s = slices[i];
+    if (!s.base || s.bytes == 0 || (s.bytes & 15u) || ((uintptr_t)s.base & 15u)) return GS_E_INVAL;
+    SliceDesc &d = b.s[i];
+    d.base = (uint4 *)s.base;
+    d.n_vec = s.bytes / 16;
+    d.tile_begin = tiles;
+    tiles += (d.n_vec + kTileVec - 1) / kTileVec;
+    d.tile_end = tiles;
+    d.seed = s.seed;
+  }
+  b.total_tiles = tiles;
+  b.n = n;
+
+  DeviceGuard g(cuda_ordinal);
+  if (!g.ok) {
+    gs_internal::set_cuda_error("cudaSetDevice", -1, "cannot select device");
+    return GS_E_CUDA;
+  }
+  DevResult *table = nullptr;
+  int sms = 0;
+  {
+    // set-up, first call on this device only, with the device current
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[cuda_ordinal]) {
+      DevResult *p = nullptr;
+      GS_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_verdicts));
+      int count = 0;
+      GS_CUDA(cudaDeviceGetAttribute(&count, cudaDevAttrMultiProcessorCount, cuda_ordinal));
+      g_noalloc_sms[cuda_ordinal] = count;
+      g_noalloc_ptr[cuda_ordinal] = p;
+    }
+    table = g_noalloc_ptr[cuda_ordinal];
+    sms = g_noalloc_sms[cuda_ordinal];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  // the table still holds the previous call's verdicts: the rows this call uses start at zero
+  GS_CUDA(cudaMemsetAsync(table, 0, sizeof(DevResult) * n, st));
+  uint64_t grid = (uint64_t)sms * 8u;
+  if (grid > tiles) grid = tiles;
+  probe_verify_kernel<4, 0><<<(int)grid, kThreads, 0, st>>>(b, table);
+  GS_CUDA(cudaGetLastError());
+  DevResult host[kNoAllocMaxSlices];
+  GS_CUDA(cudaMemcpyAsync(host, table, sizeof(DevResult) * n, cudaMemcpyDeviceToHost, st));
+  GS_CUDA(cudaStreamSynchronize(st));
+  for (uint32_t i = 0; i < n; ++i) {
+    results[i].mismatches = host[i].mismatches;
+    results[i].first_bad_byte = host[i].mismatches ? ~host[i].inv_first_bad : UINT64_MAX;
+    results[i].bit_flips = host[i].bit_flips;
+    results[i].reserved = 0;
+  }
+  return GS_OK;
+}

@@ -357,6 +357,24 @@ GS_API int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_varia
 /* Offered rate (GB/s, whole GPU) the store pass paces itself to; 0 = unpaced.
  * Default 7600: B200's write path sustains more when not over-offered.        */
 GS_API int gs_probe_set_write_rate(gs_probe *p, uint32_t gbps);
+/* Read-back pass for callers that may not allocate. No counterpart in the reference
+ * (it runs no GPU code). The plugin's health checker on a GPU whose memory is granted
+ * to tenants to the last unit cannot cudaMalloc (it would fail, or take what a tenant
+ * was promised), and some callers cannot afford cudaMalloc/cudaFree's device-wide
+ * synchronisation; this call therefore allocates nothing: the per-slice verdict table
+ * is a fixed 2 KiB array resident on every GPU that loads the library, which is why
+ * at most GS_PROBE_NOALLOC_MAX_SLICES slices fit (more => GS_E_LIMIT).
+ *   - same load+compare kernel and verdicts as gs_probe_run(..., GS_PROBE_VERIFY, ...);
+ *     the ranges must have been written before (gs_probe_submit with GS_PROBE_WRITE);
+ *   - runs on `stream` (a cudaStream_t; NULL = the default stream) of device
+ *     `cuda_ordinal` and returns after that stream has drained; no gs_probe needed;
+ *   - the first call on each device looks up the array's device address; make that
+ *     first call before starting any stream capture;
+ *   - every call on a device uses the same array and clears the rows it needs; two
+ *     calls that overlap on one GPU race on it -- serialise them.                    */
+#define GS_PROBE_NOALLOC_MAX_SLICES 64
+GS_API int gs_probe_verify_noalloc(int cuda_ordinal, void *stream, const gs_slice *slices,
+                                   uint32_t n, gs_slice_result *results);
 /* Host restatement of the pattern is NOT here: it lives in oracle/pattern.c. */
 
 #ifdef __cplusplus
