@@ -174,3 +174,30 @@ def test_large_mib_request_counts():
         assert envs == [{"NVIDIA_VISIBLE_DEVICES": "5", "ALIYUN_COM_GPU_MEM_IDX": "5",
                          "ALIYUN_COM_GPU_MEM_POD": str(n), "ALIYUN_COM_GPU_MEM_CONTAINER": str(n),
                          "ALIYUN_COM_GPU_MEM_DEV": "183359"}]
+
+
+def test_multichain_scan_is_exact_on_hostile_ids():
+    """Containers above 1 MiB are counted by several interleaved chains that start at guessed
+    record boundaries; ids full of bytes that LOOK like boundaries must not fool it."""
+    rng = random.Random(99)
+    for trial in range(24):
+        ids = []
+        for _ in range(rng.choice([300, 45000, 70000])):
+            kind = rng.random()
+            if kind < 0.4:
+                ids.append("GPU-%08x-_-%d" % (rng.randrange(2**32), rng.randrange(200000)))
+            elif kind < 0.8:      # fake records inside the id: "\n" + length byte + filler
+                ids.append("".join(rng.choice(["\n", chr(rng.randrange(1, 100)), "\n\x05abcde", "x"])
+                                   for _ in range(rng.randrange(0, 40))))
+            elif kind < 0.9:
+                ids.append("")
+            else:
+                ids.append("y" * rng.choice([127, 128, 300]))   # two-byte length prefixes
+        reqs = [ids, ["tail"]]
+        wire = R.encode_allocate_request(reqs)
+        if trial % 3 == 0:        # an unknown varint field in the middle of the container
+            inner = b"".join(R._ld(1, i.encode()) for i in ids[:len(ids) // 2]) + b"\x10\x07" + \
+                b"".join(R._ld(1, i.encode()) for i in ids[len(ids) // 2:])
+            wire = R._ld(1, inner) + R._ld(1, R._ld(1, b"tail"))
+        counts, total = api.request_scan(wire)
+        assert counts == [len(ids), 1] and total == len(ids) + 1, trial
