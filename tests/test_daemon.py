@@ -1,0 +1,70 @@
+"""The daemon's command line (cmd/nvidia/main.go:15-26) and an end-to-end run against the
+fake NVML over a real socket: BASELINE config 1."""
+import json
+import os
+import signal
+import subprocess
+import sys
+import tempfile
+import time
+
+import grpc
+import pytest
+
+from gpushare_b200 import daemon
+from gpushare_b200.grpc_harness import KubeletStub
+from oracle import ref_model as R
+from tests.conftest import FAKE_NVML, ROOT
+
+
+def test_flag_names_and_defaults_match_reference():
+    a = daemon.parse_args([])
+    assert (a.mps, a.health_check, a.memory_unit, a.query_kubelet) == (False, False, "GiB", False)
+    assert (a.kubelet_address, a.kubelet_port, a.client_cert, a.client_key, a.token, a.timeout) == \
+        ("0.0.0.0", 10250, "", "", "", 10)
+    # the DaemonSet's arguments (device-plugin-ds.yaml:29-33) and Go's single-dash form
+    a = daemon.parse_args(["-logtostderr", "--v=5", "--memory-unit=GiB"])
+    assert a.logtostderr and a.v == 5
+    a = daemon.parse_args(["-memory-unit", "MiB", "-health-check", "-query-kubelet=false", "--mps=true"])
+    assert a.memory_unit == "MiB" and a.health_check and not a.query_kubelet and a.mps
+
+
+def test_daemon_config1_end_to_end(golden_cases):
+    c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
+    with tempfile.TemporaryDirectory(prefix="gsd") as d:
+        pods = os.path.join(d, "pods.json")
+        json.dump({"items": c["pods"]}, open(pods, "w"))
+        kubelet = KubeletStub(os.path.join(d, "kubelet.sock"))
+        kubelet.start()
+        env = dict(os.environ, NODE_NAME=c["node"], FAKE_NVML_GPUS="8", FAKE_NVML_MEM_MIB="16384",
+                   PYTHONPATH=ROOT)
+        proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "-logtostderr", "--v=5",
+                                 "--memory-unit=GiB", "--nvml-lib", FAKE_NVML, "--socket-dir", d,
+                                 "--pod-source-file", pods, "--health-check"],
+                                env=env, stderr=subprocess.PIPE, text=True)
+        try:
+            assert kubelet.wait_registered(30), proc.stderr.read() if proc.poll() is not None else ""
+            ch = KubeletStub.connect(os.path.join(d, "aliyungpushare.sock"))
+            grpc.channel_ready_future(ch).result(timeout=10)
+            devs = R.decode_list_and_watch(next(KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")))
+            assert len(devs) == 128 and devs[0][0].endswith("-_-0")
+            st = c["steps"][0]
+            resp = KubeletStub.method(ch, "Allocate")(R.encode_allocate_request(st["request"]))
+            assert R.decode_allocate_response(resp) == st["expect_envs"]
+            ch.close()
+        finally:
+            proc.send_signal(signal.SIGTERM)
+            try:
+                proc.wait(10)
+            except subprocess.TimeoutExpired:
+                proc.kill()
+            kubelet.stop()
+        assert proc.returncode == 0
+
+
+def test_daemon_requires_node_name():
+    env = {k: v for k, v in os.environ.items() if k != "NODE_NAME"}
+    env["PYTHONPATH"] = ROOT
+    out = subprocess.run([sys.executable, "-m", "gpushare_b200.daemon", "--nvml-lib", FAKE_NVML],
+                         env=env, capture_output=True, text=True, timeout=60)
+    assert out.returncode != 0 and "Please set env NODE_NAME" in out.stderr
