@@ -226,6 +226,11 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("bench.py: no CUDA device; the gpushare path has no CPU fallback "
                          "(use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local_rank)
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner)
+    # are sent to stderr until the line is written
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -363,6 +368,11 @@ def run_ours(args, rank, world, local_rank):
         except OSError:
             pass
         peak, which = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        try:
+            traffic_ratio = json.load(open(os.path.join(ROOT, "profiles", "probe_traffic.json")))[
+                "traffic_over_algorithmic"]
+        except (OSError, KeyError, ValueError):
+            traffic_ratio = None
         la = totals["abi"]
         live_ms = la[4] + la[5]
         live_gbps = 2 * la[1] / (live_ms * 1e-3) / 1e9 if live_ms else 0.0
@@ -386,7 +396,10 @@ def run_ours(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "achieved": live_gbps, "peak": peak, "unit": "GB/s",
                          "frac": live_gbps / peak, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs: "
                          "torch copy_, read+write)", "frac_of_nominal_8000": live_gbps / 8000.0,
-                         "traffic": None,
+                         "traffic": (traffic_ratio * 2 * la[1] / max(la[7], 1)) if traffic_ratio else None,
+                         "traffic_source": "DRAM bytes / algorithmic bytes = %s from the ncu --set full "
+                                           "capture in profiles/probe_traffic.json, scaled to this "
+                                           "launch pair" % traffic_ratio,
                          "algorithmic_bytes_per_launch_pair": 2 * la[1] / max(la[7], 1),
                          "kernels": {"write_gbps": la[1] / (la[4] * 1e-3) / 1e9 if la[4] else 0,
                                      "verify_gbps": la[1] / (la[5] * 1e-3) / 1e9 if la[5] else 0},
@@ -407,7 +420,10 @@ def run_ours(args, rank, world, local_rank):
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(pods_k8s, wires, uuid, units)
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     probe.free(arena)
     probe.close()
     if dist is not None:

@@ -1,0 +1,57 @@
+"""Probe scheduler and the bench contract line on a real GPU."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from gpushare_b200 import _lib as L
+from tests.conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+MiB = 1 << 20
+
+
+def test_scheduler_coalesces_drains_and_reports_bad_slices():
+    from gpushare_b200.probe import Probe, ProbeScheduler
+    bad = []
+    with Probe(0) as p:
+        arena = p.alloc(64 * MiB)
+        try:
+            s = ProbeScheduler(p, on_bad=lambda tag, v: bad.append((tag, v.mismatches)))
+            for wave in range(50):                       # the same 4 ranges granted 50 times
+                for k in range(4):
+                    s.grant(arena + k * 16 * MiB, 16 * MiB, 7 + k, k)
+                s.pump()
+            s.drain()
+            assert s.inflight is None and not s.pending
+            assert s.bytes_granted == 50 * 64 * MiB
+            assert 0 < s.bytes_probed <= s.bytes_granted and s.bytes_probed % (16 * MiB) == 0
+            assert s.coalesced > 0 and s.dropped == 0 and s.bad == 0 and s.launches == 2 * s.batches
+            assert s.gbps() > 100
+            # a verify-only sweep over a range someone scribbled on reports through on_bad
+            p.inject(arena + 16 * MiB, 4096, 0x1)
+            v, _ = p.run([(arena + 16 * MiB, 16 * MiB, 8, 1)], L.GS_PROBE_VERIFY)
+            assert v[0].mismatches == 1
+            s2 = ProbeScheduler(p, on_bad=lambda tag, v: bad.append((tag, v.mismatches)))
+            s2.grant(arena, 16 * MiB, 7, 0)
+            s2.drain()
+            assert s2.bad == 0 and bad == []             # a fresh write+verify is clean again
+        finally:
+            p.free(arena)
+
+
+def test_bench_line_contract():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "2", "--warmup", "3",
+                          "--no-cpu-baseline"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-3000:]
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+                "scaling", "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "roofline",
+                "clocks"):
+        assert key in r, key
+    assert r["metric"] == "allocate_decisions_per_s" and r["n_gpus"] == 1 and r["steps"] == 2
+    assert r["value"] > 1000 and r["e2e"]["value"] > 500 and r["gpu_launches"] >= 2
+    assert r["roofline"]["bound"] == "hbm" and r["roofline"]["achieved"] > 3000
+    assert r["probe"]["bad_slices"] == 0 and "workload" in r["config"]
