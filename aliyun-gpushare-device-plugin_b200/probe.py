@@ -108,6 +108,20 @@ class Probe:
         self.submit(slices, passes)
         return self.wait()
 
+    def sweep_free(self, margin_bytes=2 << 30, seed=0x5EED):
+        """Health-time probe: sweep everything that is free right now minus a margin
+        (tenants' memory is theirs; only unallocated HBM can be written)."""
+        free, _total = self.mem_info()
+        nbytes = (free - margin_bytes) & ~0xFFFFF
+        if nbytes <= 0:
+            return None, None
+        d = self.alloc(nbytes)
+        try:
+            verdicts, tm = self.run([(d, nbytes, seed)])
+        finally:
+            self.free(d)
+        return verdicts[0], tm
+
     def inject(self, base, byte_offset, mask):
         L.check(self.lib.gs_probe_inject(self.h, C.c_void_p(base), byte_offset, mask),
                 "gs_probe_inject")

@@ -20,7 +20,9 @@
  *   - strings are (pointer,length) pairs unless documented as NUL-terminated;
  *   - gs_table is immutable after gs_table_build except for its health bits,
  *     which are atomics: concurrent readers need no lock;
- *   - gs_allocate and gs_plugin_allocate perform no heap allocation;
+ *   - gs_allocate and gs_plugin_allocate perform no heap allocation in steady state
+ *     (per-thread scratch grows once to the largest pod list seen);
+ *   - a gs_probe serves one caller at a time (one batch in flight); use one per GPU;
  *   - pod *claiming* must be serialised by the caller exactly as the
  *     reference's m.Lock() does (allocate.go:60-61); gs_plugin_* does that
  *     internally with one mutex.

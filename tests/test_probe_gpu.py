@@ -168,3 +168,19 @@ def test_nvml_enumeration_and_ordinal_map():
 def test_smoke_entry():
     import __graft_entry__
     __graft_entry__.smoke()
+
+
+def test_real_nvml_health_watch_opens_and_times_out():
+    """The XID watch against the real driver: register on every GPU, no event within 200 ms."""
+    from gpushare_b200 import api
+    with api.Nvml() as nv:
+        mask = nv.health_open()
+        assert mask == 0                                  # B200 supports XID events
+        assert nv.health_wait(200) is None
+        nv.health_close()
+
+
+def test_health_time_sweep_of_free_memory(probe):
+    v, tm = probe.sweep_free(margin_bytes=4 << 30)
+    assert v is not None and v.clean
+    assert tm.bytes > 100 << 30 and tm.gbps() > 5000       # most of a B200, at HBM speed
