@@ -5,11 +5,11 @@ Go's `flag` accepts) and environment (NODE_NAME mandatory, podmanager.go:55-58),
 the hot path: NVML enumerate -> device table -> plugin -> gRPC server -> Register ->
 XID health watch -> probe at Allocate time.
 
-Out of scope here: the apiserver/kubelet pod lister and patcher and
-the fsnotify/signal supervisor. The pod source is therefore a JSON file of pods in the
-Kubernetes shape (--pod-source-file, re-read on every Allocate), which is what the test
-harness and the benchmarks drive; a cluster deployment plugs a real lister into
-`PodSourceFile`'s place.
+Pod source: by default the live one (k8s_io: kubelet /pods or apiserver LIST with the
+reference's retry ladders, PATCH with its one retry; KUBECONFIG or the in-cluster service
+account). With --pod-source-file the pods come from a JSON file in the Kubernetes shape,
+re-read on every Allocate, which is what the test harness drives. The fsnotify/SIGHUP
+supervisor loop (gpumanager.go:63-108) is not built.
 
     python -m gpushare_b200.daemon --memory-unit=MiB --health-check --pod-source-file pods.json
 """
@@ -106,8 +106,29 @@ def main(argv=None):
         log(a.v, 1, "No devices found. Waiting indefinitely.")
         threading.Event().wait()                                    # gpumanager.go:44-47
     table = api.DeviceTable.from_gpus(infos, unit)                  # getDevices
-    plugin = api.NvidiaDevicePlugin(table, node)
-    source = PodSourceFile(a.pod_source_file)
+    source = None
+    if a.pod_source_file:
+        plugin = api.NvidiaDevicePlugin(table, node)
+        source = PodSourceFile(a.pod_source_file)
+    else:
+        from . import k8s_io
+        token = a.token
+        if not (a.client_cert or a.client_key or token):           # main.go:28-36
+            try:
+                token = open(k8s_io.SA_DIR + "/token").read()
+            except OSError as e:
+                sys.exit("in cluster mode, find token failed, error: %s" % e)
+        transport = k8s_io.HttpTransport(
+            k8s_io.ApiConfig.load(), "https://%s:%d" % (a.kubelet_address, a.kubelet_port), token,
+            a.client_cert or None, a.client_key or None, timeout=float(a.timeout))
+        try:                                                       # server.go:57-64
+            k8s_io.patch_gpu_count(transport, node, len(infos))
+            cgpu = k8s_io.disable_cgpu_isolation_or_not(transport, node)
+        except Exception as e:
+            log(a.v, 0, "Failed to get device plugin due to %s" % e)
+            sys.exit(1)                                            # gpumanager.go:71-73
+        plugin = k8s_io.ClusterDevicePlugin(
+            table, node, k8s_io.PodLister(transport, node, a.query_kubelet), transport, cgpu)
 
     probes = {}
     if a.probe:
@@ -121,7 +142,8 @@ def main(argv=None):
     arenas = {}
 
     def refresh_pods_then_allocate(request, _orig=plugin.Allocate):
-        plugin.set_pods(source.list())
+        if source is not None:
+            plugin.set_pods(source.list())
         d = _orig(request)
         sched = probes.get(d.gpu_index)
         if sched is not None and d.kind == "matched":

@@ -812,3 +812,84 @@ def decode_list_and_watch(buf: bytes):
                 h = x.decode()
         out.append((i, h))
     return out
+
+
+# --- N1: the lister's retry ladders (podmanager.go:187-245) -------------------------------
+retries = 8  # podmanager.go:29
+
+
+class LadderPodSource(PodSource):
+    """The reference's real pod source with its I/O abstracted: `transport` supplies
+    kubelet_pods() -> PodList dict (pkg/kubelet/client/client.go:119-134),
+    api_list(field_selector, label_selector) -> PodList dict (podmanager.go:229) and
+    api_patch(namespace, name, body) (allocate.go:136); `sleep(seconds)` is time.Sleep.
+    Every transport call may raise. Drop-in for PodSource under NvidiaDevicePlugin."""
+
+    def __init__(self, transport, sleep, nodeName, queryKubelet):
+        self.t = transport
+        self.sleep = sleep
+        self.nodeName = nodeName
+        self.queryKubelet = queryKubelet
+        self.patches = []
+
+    def getPodList(self):
+        """podmanager.go:187-208."""
+        podList = self.t.kubelet_pods()
+        items = [p for p in (podList.get("items") or [])
+                 if ((p.get("status") or {}).get("phase")) == "Pending"]
+        if len(items) == 0:
+            raise RuntimeError("not found pending pod")
+        return {"items": items}
+
+    def getPodListsByQueryKubelet(self):
+        """podmanager.go:210-225: first try, then up to `retries` more, each followed by a
+        100 ms sleep (the sleep also follows the try that finally succeeds)."""
+        podList, err = None, None
+        try:
+            podList = self.getPodList()
+        except Exception as e:
+            err = e
+        i = 0
+        while i < retries and err is not None:
+            try:
+                podList, err = self.getPodList(), None
+            except Exception as e:
+                err = e
+            self.sleep(0.1)
+            i += 1
+        if err is not None:
+            podList = self.getPodListsByListAPIServer()
+        return podList
+
+    def getPodListsByListAPIServer(self):
+        """podmanager.go:227-245: fields.SelectorFromSet sorts its keys; first try plus up to
+        three more, each followed by a 1 s sleep."""
+        selector = "spec.nodeName=%s,status.phase=Pending" % self.nodeName
+        podList, err = None, None
+        try:
+            podList = self.t.api_list(selector, "")
+        except Exception as e:
+            err = e
+        i = 0
+        while i < 3 and err is not None:
+            try:
+                podList, err = self.t.api_list(selector, ""), None
+            except Exception as e:
+                err = e
+            self.sleep(1.0)
+            i += 1
+        if err is not None:
+            raise RuntimeError("failed to get Pods assigned to node %s" % self.nodeName)
+        return podList
+
+    def list_pending(self):
+        """podmanager.go:256-267."""
+        if self.queryKubelet:
+            podList = self.getPodListsByQueryKubelet()
+        else:
+            podList = self.getPodListsByListAPIServer()
+        return copy.deepcopy(podList.get("items") or [])
+
+    def patch(self, namespace, name, body: bytes):
+        self.t.api_patch(namespace, name, body)
+        self.patches.append((namespace, name, body))
