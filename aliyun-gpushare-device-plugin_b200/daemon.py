@@ -8,17 +8,26 @@ XID health watch -> probe at Allocate time.
 Pod source: by default the live one (k8s_io: kubelet /pods or apiserver LIST with the
 reference's retry ladders, PATCH with its one retry; KUBECONFIG or the in-cluster service
 account). With --pod-source-file the pods come from a JSON file in the Kubernetes shape,
-re-read on every Allocate, which is what the test harness drives. The fsnotify/SIGHUP
-supervisor loop (gpumanager.go:63-108) is not built.
+re-read on every Allocate, which is what the test harness drives.
+
+Supervisor (gpumanager.go:33-111, watchers.go): the plugin instance is torn down, devices
+re-enumerated and registration repeated when kubelet.sock is re-created in the
+device-plugins directory (kubelet restart) or on SIGHUP; SIGQUIT dumps every thread's
+stack to /etc/kubernetes/go_<timestamp>.txt; SIGINT/SIGTERM stop the plugin and exit 0.
 
     python -m gpushare_b200.daemon --memory-unit=MiB --health-check --pod-source-file pods.json
 """
 import argparse
+import ctypes
+import faulthandler
 import json
 import os
+import select
 import signal
+import struct
 import sys
 import threading
+import time
 
 from . import _lib as L
 from . import api
@@ -84,6 +93,156 @@ def log(v, level, msg):
         print(msg, file=sys.stderr, flush=True)
 
 
+class FSWatcher:
+    """newFSWatcher (watchers.go:10-25): inotify on the device-plugins directory."""
+    IN_CREATE = 0x100
+
+    def __init__(self, path):
+        self.libc = ctypes.CDLL(None, use_errno=True)
+        self.fd = self.libc.inotify_init1(os.O_NONBLOCK | os.O_CLOEXEC)
+        if self.fd < 0:
+            raise OSError(ctypes.get_errno(), "inotify_init1")
+        if self.libc.inotify_add_watch(self.fd, path.encode(), self.IN_CREATE) < 0:
+            err = ctypes.get_errno()
+            os.close(self.fd)
+            raise OSError(err, "inotify_add_watch(%s)" % path)
+
+    def events(self):
+        """-> [(file name, mask)] that arrived since the last call."""
+        out = []
+        try:
+            buf = os.read(self.fd, 65536)
+        except BlockingIOError:
+            return out
+        off = 0
+        while off + 16 <= len(buf):
+            _wd, mask, _cookie, ln = struct.unpack_from("iIII", buf, off)
+            name = buf[off + 16:off + 16 + ln].split(b"\0", 1)[0].decode()
+            out.append((name, mask))
+            off += 16 + ln
+        return out
+
+    def close(self):
+        os.close(self.fd)
+
+
+class PluginInstance:
+    """One NewNvidiaDevicePlugin + Serve (gpumanager.go:70-79): everything that is rebuilt on
+    a restart."""
+
+    def __init__(self, a, nv, unit, node):
+        self.a, self.nv = a, nv
+        infos = nv.devices()
+        self.infos = infos
+        self.table = api.DeviceTable.from_gpus(infos, unit)         # getDevices
+        self.source = None
+        if a.pod_source_file:
+            self.plugin = api.NvidiaDevicePlugin(self.table, node)
+            self.source = PodSourceFile(a.pod_source_file)
+        else:
+            from . import k8s_io
+            token = a.token
+            if not (a.client_cert or a.client_key or token):        # main.go:28-36
+                try:
+                    token = open(k8s_io.SA_DIR + "/token").read()
+                except OSError as e:
+                    sys.exit("in cluster mode, find token failed, error: %s" % e)
+            transport = k8s_io.HttpTransport(
+                k8s_io.ApiConfig.load(), "https://%s:%d" % (a.kubelet_address, a.kubelet_port), token,
+                a.client_cert or None, a.client_key or None, timeout=float(a.timeout))
+            try:                                                    # server.go:57-64
+                k8s_io.patch_gpu_count(transport, node, len(infos))
+                cgpu = k8s_io.disable_cgpu_isolation_or_not(transport, node)
+            except Exception as e:
+                log(a.v, 0, "Failed to get device plugin due to %s" % e)
+                sys.exit(1)                                         # gpumanager.go:71-73
+            self.plugin = k8s_io.ClusterDevicePlugin(
+                self.table, node, k8s_io.PodLister(transport, node, a.query_kubelet), transport, cgpu)
+
+        self.probes = {}
+        if a.probe:
+            from .probe import Probe, ProbeScheduler
+            for info, o in zip(infos, nv.map_cuda_ordinals(infos)):
+                if o >= 0:
+                    self.probes[info.nvml_index] = ProbeScheduler(
+                        Probe(o), on_bad=lambda tag, v, g=info.nvml_index: self.plugin.unhealthy(g))
+        self.unit_bytes = (1 << 20) if unit == api.MiB else (1 << 30)
+        self.arenas = {}
+        self._allocate = self.plugin.Allocate
+        self.plugin.Allocate = self.allocate_and_probe
+        self.server = DevicePluginServer(
+            self.plugin, os.path.join(a.socket_dir, os.path.basename(SERVER_SOCK)))
+        self.stop = threading.Event()
+
+    def allocate_and_probe(self, request):
+        if self.source is not None:
+            self.plugin.set_pods(self.source.list())
+        d = self._allocate(request)
+        sched = self.probes.get(d.gpu_index)
+        if sched is not None and d.kind == "matched":
+            # exactly the granted range, capped by what is free right now; a failed
+            # allocation never changes the answer (parity)
+            nbytes = d.pod_req_units * self.unit_bytes
+            try:
+                free, _ = sched.probe.mem_info()
+                nbytes = min(nbytes, max(0, free - (1 << 30))) & ~0xFFFFF
+                if nbytes:
+                    old = self.arenas.pop(d.gpu_index, None)
+                    sched.drain()
+                    if old:
+                        sched.probe.free(old)
+                    self.arenas[d.gpu_index] = sched.probe.alloc(nbytes)
+                    sched.grant(self.arenas[d.gpu_index], nbytes, d.pod_index & 0xFFFFFFFF, d.pod_index)
+                    sched.pump()
+            except L.GpushareError as e:
+                log(self.a.v, 1, "probe skipped: %s" % e)
+        return d
+
+    def Serve(self):
+        a = self.a
+        if a.no_register:
+            self.server.Start()
+        else:
+            self.server.Serve(os.path.join(a.socket_dir, os.path.basename(KUBELET_SOCKET)))
+        log(a.v, 1, "Starting to serve on %s" % self.server.socket)
+        if a.health_check:                                          # server.go:211-229
+            bad_mask = self.nv.health_open()
+            for g in range(len(self.infos)):
+                if bad_mask >> g & 1:
+                    self.plugin.unhealthy(g)                        # nvidia.go:107-111
+
+            def pump():
+                while not self.stop.is_set():
+                    ev = self.nv.health_wait(1000)
+                    if ev and not ev[2]:
+                        self.plugin.unhealthy(ev[0])
+                    for s in self.probes.values():
+                        s.pump()
+            self.pump_thread = threading.Thread(target=pump, daemon=True)
+            self.pump_thread.start()
+
+    def Stop(self):
+        self.stop.set()
+        self.server.Stop()
+        if self.a.health_check:
+            self.pump_thread.join(3)
+            self.nv.health_close()
+        for g, sched in self.probes.items():
+            sched.drain()
+            if g in self.arenas:
+                sched.probe.free(self.arenas[g])
+            sched.probe.close()
+
+
+def coredump(path):
+    """coredump.go:10-30, for threads instead of goroutines."""
+    try:
+        with open(path, "w") as f:
+            faulthandler.dump_traceback(file=f, all_threads=True)
+    except OSError as e:
+        print("failed to write %s: %s" % (path, e), file=sys.stderr)
+
+
 def main(argv=None):
     a = parse_args(argv)
     unit, warned = api.translate_memory_units(a.memory_unit)       # main.go:67-78
@@ -93,115 +252,59 @@ def main(argv=None):
     if not node:
         sys.exit("Please set env NODE_NAME")                        # podmanager.go:55-58
     log(a.v, 1, "Start gpushare device plugin")
+    # ---- sharedGPUManager.Run (gpumanager.go:33-111) ---------------------------------
     log(a.v, 1, "Loading NVML")
     try:
-        nv = api.Nvml(a.nvml_lib or None)                           # gpumanager.go:36
+        nv = api.Nvml(a.nvml_lib or None)                           # :36
     except L.GpushareError as e:
         log(a.v, 1, "Failed to initialize NVML: %s." % e)
         log(a.v, 1, "If this is a GPU node, did you set the docker default runtime to `nvidia`?")
-        threading.Event().wait()                                    # select {} (gpumanager.go:39)
+        threading.Event().wait()                                    # select {} (:39)
     log(a.v, 1, "Fetching devices.")
-    infos = nv.devices()
-    if len(infos) == 0:
+    if nv.device_count() == 0:
         log(a.v, 1, "No devices found. Waiting indefinitely.")
-        threading.Event().wait()                                    # gpumanager.go:44-47
-    table = api.DeviceTable.from_gpus(infos, unit)                  # getDevices
-    source = None
-    if a.pod_source_file:
-        plugin = api.NvidiaDevicePlugin(table, node)
-        source = PodSourceFile(a.pod_source_file)
-    else:
-        from . import k8s_io
-        token = a.token
-        if not (a.client_cert or a.client_key or token):           # main.go:28-36
+        threading.Event().wait()                                    # :44-47
+    log(a.v, 1, "Starting FS watcher.")
+    watcher = FSWatcher(a.socket_dir)                               # :50
+    log(a.v, 1, "Starting OS watcher.")
+    rd, wr = os.pipe()                                              # newOSWatcher (watchers.go:27-32)
+    os.set_blocking(wr, False)
+    for s in (signal.SIGHUP, signal.SIGINT, signal.SIGTERM, signal.SIGQUIT):
+        signal.signal(s, lambda signum, _f: os.write(wr, bytes([signum])))
+    kubelet_sock = os.path.basename(KUBELET_SOCKET)
+    restart, inst = True, None
+    while True:
+        if restart:                                                 # :66-79
+            if inst is not None:
+                inst.Stop()
+            inst = PluginInstance(a, nv, unit, node)
             try:
-                token = open(k8s_io.SA_DIR + "/token").read()
-            except OSError as e:
-                sys.exit("in cluster mode, find token failed, error: %s" % e)
-        transport = k8s_io.HttpTransport(
-            k8s_io.ApiConfig.load(), "https://%s:%d" % (a.kubelet_address, a.kubelet_port), token,
-            a.client_cert or None, a.client_key or None, timeout=float(a.timeout))
-        try:                                                       # server.go:57-64
-            k8s_io.patch_gpu_count(transport, node, len(infos))
-            cgpu = k8s_io.disable_cgpu_isolation_or_not(transport, node)
-        except Exception as e:
-            log(a.v, 0, "Failed to get device plugin due to %s" % e)
-            sys.exit(1)                                            # gpumanager.go:71-73
-        plugin = k8s_io.ClusterDevicePlugin(
-            table, node, k8s_io.PodLister(transport, node, a.query_kubelet), transport, cgpu)
-
-    probes = {}
-    if a.probe:
-        from .probe import Probe, ProbeScheduler
-        for info, o in zip(infos, nv.map_cuda_ordinals(infos)):
-            if o >= 0:
-                probes[info.nvml_index] = ProbeScheduler(
-                    Probe(o), on_bad=lambda tag, v, g=info.nvml_index: plugin.unhealthy(g))
-
-    unit_bytes = (1 << 20) if unit == api.MiB else (1 << 30)
-    arenas = {}
-
-    def refresh_pods_then_allocate(request, _orig=plugin.Allocate):
-        if source is not None:
-            plugin.set_pods(source.list())
-        d = _orig(request)
-        sched = probes.get(d.gpu_index)
-        if sched is not None and d.kind == "matched":
-            # exactly the granted range, capped by what is free right now; never lets a
-            # failed allocation change the answer (parity)
-            nbytes = d.pod_req_units * unit_bytes
-            try:
-                free, _ = sched.probe.mem_info()
-                nbytes = min(nbytes, max(0, free - (1 << 30))) & ~0xFFFFF
-                if nbytes:
-                    old = arenas.pop(d.gpu_index, None)
-                    sched.drain()
-                    if old:
-                        sched.probe.free(old)
-                    arenas[d.gpu_index] = sched.probe.alloc(nbytes)
-                    sched.grant(arenas[d.gpu_index], nbytes, d.pod_index & 0xFFFFFFFF, d.pod_index)
-                    sched.pump()
-            except L.GpushareError as e:
-                log(a.v, 1, "probe skipped: %s" % e)
-        return d
-
-    plugin.Allocate = refresh_pods_then_allocate
-    server = DevicePluginServer(plugin, os.path.join(a.socket_dir, os.path.basename(SERVER_SOCK)))
-    if a.no_register:
-        server.Start()
-    else:
-        try:
-            server.Serve(os.path.join(a.socket_dir, os.path.basename(KUBELET_SOCKET)))
-        except Exception as e:
-            log(a.v, 0, "Failed to start device plugin due to %s" % e)
-            sys.exit(2)                                             # gpumanager.go:74-76
-    log(a.v, 1, "Starting to serve on %s" % server.socket)
-
-    stop = threading.Event()
-    if a.health_check:                                              # server.go:211-229
-        bad_mask = nv.health_open()
-        for g in range(len(infos)):
-            if bad_mask >> g & 1:
-                plugin.unhealthy(g)                                 # nvidia.go:107-111
-
-        def pump():
-            while not stop.is_set():
-                ev = nv.health_wait(5000)                           # nvidia.go:125
-                if ev and not ev[2]:
-                    plugin.unhealthy(ev[0])
-                for s in probes.values():
-                    s.pump()
-        threading.Thread(target=pump, daemon=True).start()
-
-    def on_signal(signum, _frame):                                  # gpumanager.go:102-106
-        log(a.v, 1, 'Received signal "%d", shutting down.' % signum)
-        stop.set()
-    for s in (signal.SIGINT, signal.SIGTERM):
-        signal.signal(s, on_signal)
-    stop.wait()
-    server.Stop()
-    nv.close()
+                inst.Serve()
+            except Exception as e:
+                log(a.v, 0, "Failed to start device plugin due to %s" % e)
+                sys.exit(2)                                         # :74-76
+            restart = False
+        ready, _, _ = select.select([watcher.fd, rd], [], [], 1.0)
+        if watcher.fd in ready:
+            for name, mask in watcher.events():                     # :82-87
+                if name == kubelet_sock and mask & FSWatcher.IN_CREATE:
+                    log(a.v, 1, "inotify: %s created, restarting." % KUBELET_SOCKET)
+                    restart = True
+        if rd in ready:
+            for signum in os.read(rd, 64):
+                if signum == signal.SIGHUP:                         # :94-96
+                    log(a.v, 1, "Received SIGHUP, restarting.")
+                    restart = True
+                elif signum == signal.SIGQUIT:                      # :97-101
+                    log(a.v, 0, "generate core dump")
+                    coredump("/etc/kubernetes/go_" + time.strftime("%Y%m%d%H%M%S") + ".txt")
+                else:                                               # :102-106
+                    log(a.v, 1, 'Received signal "%d", shutting down.' % signum)
+                    inst.Stop()
+                    watcher.close()
+                    log(a.v, 1, "Shutdown of NVML returned: %s" % nv.close())
+                    return 0
 
 
 if __name__ == "__main__":
-    main()
+    sys.exit(main())

@@ -68,3 +68,48 @@ def test_daemon_requires_node_name():
     out = subprocess.run([sys.executable, "-m", "gpushare_b200.daemon", "--nvml-lib", FAKE_NVML],
                          env=env, capture_output=True, text=True, timeout=60)
     assert out.returncode != 0 and "Please set env NODE_NAME" in out.stderr
+
+
+def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases):
+    """gpumanager.go:83-96: kubelet.sock re-created => tear down, re-enumerate, register again;
+    SIGHUP => the same."""
+    c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
+    with tempfile.TemporaryDirectory(prefix="gsd") as d:
+        pods = os.path.join(d, "pods.json")
+        json.dump({"items": c["pods"]}, open(pods, "w"))
+        kubelet = KubeletStub(os.path.join(d, "kubelet.sock"))
+        kubelet.start()
+        env = dict(os.environ, NODE_NAME=c["node"], FAKE_NVML_GPUS="2", FAKE_NVML_MEM_MIB="4096",
+                   PYTHONPATH=ROOT)
+        proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "--v=1", "--nvml-lib", FAKE_NVML,
+                                 "--socket-dir", d, "--pod-source-file", pods],
+                                env=env, stderr=subprocess.PIPE, text=True)
+        try:
+            assert kubelet.wait_registered(30)
+            # kubelet restarts: its socket disappears and comes back
+            kubelet.stop()
+            time.sleep(0.3)
+            kubelet2 = KubeletStub(os.path.join(d, "kubelet.sock"))
+            kubelet2.start()
+            assert kubelet2.wait_registered(15), "no re-registration after kubelet.sock was re-created"
+            n_before = len(kubelet2.registered)
+            proc.send_signal(signal.SIGHUP)
+            deadline = time.time() + 15
+            while len(kubelet2.registered) == n_before and time.time() < deadline:
+                time.sleep(0.05)
+            assert len(kubelet2.registered) == n_before + 1, "no re-registration after SIGHUP"
+            ch = KubeletStub.connect(os.path.join(d, "aliyungpushare.sock"))
+            grpc.channel_ready_future(ch).result(timeout=10)
+            devs = R.decode_list_and_watch(next(KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")))
+            assert len(devs) == 8                        # 2 GPUs x 4 GiB
+            ch.close()
+            kubelet2.stop()
+        finally:
+            proc.send_signal(signal.SIGTERM)
+            try:
+                proc.wait(10)
+            except subprocess.TimeoutExpired:
+                proc.kill()
+        assert proc.returncode == 0
+        err = proc.stderr.read()
+        assert "kubelet.sock created, restarting." in err and "Received SIGHUP, restarting." in err
