@@ -1,0 +1,122 @@
+"""N3 (kubectl-inspect-gpushare) and N4 (manifests) -- SURVEY 8(f)."""
+import os
+
+import yaml
+
+from gpushare_b200 import inspect_gpushare as I
+from tests.conftest import ROOT
+
+
+def node(name, ip, mem, count):
+    return {"metadata": {"name": name},
+            "status": {"allocatable": {"aliyun.com/gpu-mem": str(mem), "aliyun.com/gpu-count": str(count)},
+                       "addresses": [{"type": "Hostname", "address": name},
+                                     {"type": "InternalIP", "address": ip}]}}
+
+
+def pod(name, ns, node_name, limit, idx=None, phase="Running", extra=None):
+    ann = dict(extra or {})
+    if idx is not None:
+        ann["ALIYUN_COM_GPU_MEM_IDX"] = idx
+    return {"metadata": {"uid": "u-" + name, "name": name, "namespace": ns, "annotations": ann},
+            "spec": {"nodeName": node_name, "containers": [
+                {"resources": {"limits": {"aliyun.com/gpu-mem": str(limit)}}}]},
+            "status": {"phase": phase}}
+
+
+NODES = [node("node-a", "10.0.0.5", 358, 2)]
+PODS = [pod("train", "default", "node-a", 40, "0"), pod("infer", "team-b", "node-a", 10, "1"),
+        pod("pending", "default", "node-a", 5, None, extra={"x": "y"}),
+        pod("elsewhere", "default", "node-b", 7, "0"), pod("cpu-only", "default", "node-a", 0, None)]
+
+
+def test_tabwriter_column_blocks():
+    # widths are per block of consecutive lines that HAVE the column; the text after the last
+    # tab is never padded; a line without tabs ends every block
+    text = "a\tbbb\tc\nxxxx\ty\tz\nno tabs here\nlonger-cell\tq\n"
+    assert I.tabwrite(text) == ("a     bbb  c\n"
+                                "xxxx  y    z\n"
+                                "no tabs here\n"
+                                "longer-cell  q\n")
+    assert I.tabwrite("x\t\n") == "x  \n"          # one tab-terminated cell, empty tail
+
+
+def test_summary_table_hand_derived():
+    """display.go:141-245 laid out by hand: columns are 8, 11, 23, 23 and 20 wide."""
+    infos, unit = I.build_all_node_infos(PODS, NODES)
+    assert unit == "GiB"                            # the reference would say MiB (179 > 100)
+    got = I.display_summary(infos, unit)
+    want = ("NAME" + " " * 4 + "IPADDRESS" + " " * 2 + "GPU0(Allocated/Total)" + " " * 2 +
+            "GPU1(Allocated/Total)" + " " * 2 + "PENDING(Allocated)" + " " * 2 + "GPU Memory(GiB)\n" +
+            "node-a" + " " * 2 + "10.0.0.5" + " " * 3 + "40/179" + " " * 17 + "10/179" + " " * 17 +
+            "5" + " " * 19 + "55/358\n" +
+            "-" * 59 + "\n" +
+            "Allocated/Total GPU Memory In Cluster:\n" +
+            "55/358 (15%)  \n")
+    assert got == want
+
+
+def test_details_table_hand_derived():
+    """display.go:15-129: the pod rows form one block with the header row."""
+    infos, _ = I.build_all_node_infos(PODS, NODES)
+    got = I.display_details(infos)
+    # the "Allocated :" and "Total :" lines follow the pod rows directly, so they belong to
+    # the same blocks for the first two columns: widths 13 ("Allocated :" + 2) and 11
+    rows = ("NAME" + " " * 9 + "NAMESPACE" + " " * 2 + "GPU0(Allocated)" + " " * 2 + "GPU1(Allocated)" + " " * 2 +
+            "Pending(Allocated)" + " " * 2 + "\n" +
+            "train" + " " * 8 + "default" + " " * 4 + "40" + " " * 15 + "0" + " " * 16 + "0" + " " * 19 + "\n" +
+            "infer" + " " * 8 + "team-b" + " " * 5 + "0" + " " * 16 + "10" + " " * 15 + "0" + " " * 19 + "\n" +
+            "pending" + " " * 6 + "default" + " " * 4 + "0" + " " * 16 + "0" + " " * 16 + "5" + " " * 19 + "\n" +
+            "Allocated :" + " " * 2 + "55 (15%)" + " " * 3 + "\n" +
+            "Total :" + " " * 6 + "358 " + " " * 7 + "\n")
+    assert got.startswith("\nNAME:       node-a\nIPADDRESS:  10.0.0.5\n\n")
+    assert rows in got
+    assert got.endswith("Allocated/Total GPU Memory In Cluster:  55/358 (15%)  \n")
+    # raw (pre-layout) pod rows incl. tabs and newline: train 22 + infer 21 + pending 23, + 10
+    assert "\n" + "-" * 76 + "\n" in got and "-" * 77 not in got
+
+
+def test_allocation_annotation_and_unit_guess():
+    alloc = {"scheduler.framework.gpushare.allocation": '{"0": {"0": 3, "1": 4}, "1": {"1": 2}}'}
+    p = pod("multi", "default", "node-a", 9, "0", extra=alloc)
+    assert I.get_allocation(p) == {0: 3, 1: 6}
+    infos, _ = I.build_all_node_infos([p], NODES)
+    assert (infos[0].devs[0].used, infos[0].devs[1].used) == (3, 6)
+    assert I.get_allocation(pod("bad", "d", "n", 1, extra={"scheduler.framework.gpushare.allocation": "{"})) == {}
+    assert I.guess_unit(8 * 183359, 8) == "MiB" and I.guess_unit(8 * 179, 8) == "GiB"
+    assert I.guess_unit(8 * 16, 8) == "GiB" and I.guess_unit(5, 0) == ""
+    assert [p["metadata"]["name"] for p in I.filter_active_pods(
+        [pod("a", "d", "n", 1, phase="Succeeded"), pod("b", "d", "n", 1, phase="Failed"),
+         pod("c", "d", "n", 1, phase="Pending")])] == ["c"]
+
+
+def test_manifests_keep_the_drop_in_names():
+    """device-plugin-ds.yaml / device-plugin-rbac.yaml of the reference, name for name."""
+    ds = yaml.safe_load(open(os.path.join(ROOT, "deploy", "gpushare-b200-daemonset.yaml")))
+    assert (ds["kind"], ds["metadata"]["name"], ds["metadata"]["namespace"]) == \
+        ("DaemonSet", "gpushare-device-plugin-ds", "kube-system")
+    labels = {"component": "gpushare-device-plugin", "app": "gpushare", "name": "gpushare-device-plugin-ds"}
+    assert ds["spec"]["selector"]["matchLabels"] == labels == ds["spec"]["template"]["metadata"]["labels"]
+    spec = ds["spec"]["template"]["spec"]
+    assert spec["serviceAccount"] == "gpushare-device-plugin" and spec["hostNetwork"] is True
+    assert spec["nodeSelector"] == {"gpushare": "true"}
+    c = spec["containers"][0]
+    assert c["command"][:4] == ["gpushare-device-plugin-v2", "-logtostderr", "--v=5", "--memory-unit=GiB"]
+    env = {e["name"]: e for e in c["env"]}
+    assert env["KUBECONFIG"]["value"] == "/etc/kubernetes/kubelet.conf"
+    assert env["NODE_NAME"]["valueFrom"]["fieldRef"]["fieldPath"] == "spec.nodeName"
+    assert c["volumeMounts"][0]["mountPath"] == spec["volumes"][0]["hostPath"]["path"] == \
+        "/var/lib/kubelet/device-plugins"
+    assert c["resources"]["limits"] == c["resources"]["requests"]
+    # the daemon accepts exactly these arguments
+    from gpushare_b200 import daemon
+    a = daemon.parse_args(c["command"][1:])
+    assert a.memory_unit == "GiB" and a.health_check and a.v == 5
+    docs = list(yaml.safe_load_all(open(os.path.join(ROOT, "deploy", "gpushare-b200-rbac.yaml"))))
+    kinds = {d["kind"]: d for d in docs}
+    assert set(kinds) == {"ClusterRole", "ServiceAccount", "ClusterRoleBinding"}
+    assert all(d["metadata"]["name"] == "gpushare-device-plugin" for d in docs)
+    rules = {tuple(r["resources"]): set(r["verbs"]) for r in kinds["ClusterRole"]["rules"]}
+    assert {"patch", "list", "get"} <= rules[("pods",)] and "patch" in rules[("nodes/status",)]
+    assert "get" in rules[("nodes", "nodes/proxy")]
+    assert kinds["ClusterRoleBinding"]["subjects"][0]["namespace"] == "kube-system"
