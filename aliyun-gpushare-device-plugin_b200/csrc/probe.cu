@@ -74,6 +74,35 @@ __device__ __forceinline__ uint4 slice_pattern(uint64_t i, uint32_t seed) {
   return v;
 }
 
+// The same function, split for the kernels' inner loops: a tile is 4096 words and starts
+// on a multiple of 4096, so the high index word and everything derived from it and the
+// seed are constant across a tile and are folded once per tile; per word one multiply-add,
+// the avalanche, and the three derived words remain. Bit-identical to slice_pattern.
+struct TilePattern {
+  uint32_t base;  // (hi ^ seed) * 0x85EBCA77 + seed
+  uint32_t hic;   // hi ^ 0xC2B2AE3D
+  uint32_t lo0;   // low index word of the tile's first word
+  __device__ __forceinline__ TilePattern(uint64_t v0, uint32_t seed) {
+    const uint32_t hi = (uint32_t)(v0 >> 32);
+    base = (hi ^ seed) * 0x85EBCA77u + seed;
+    hic = hi ^ 0xC2B2AE3Du;
+    lo0 = (uint32_t)v0;
+  }
+  __device__ __forceinline__ uint4 word(uint32_t j) const {  // j < kTileVec
+    const uint32_t lo = lo0 + j;
+    uint32_t h = lo * 0x9E3779B1u + base;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    h ^= h >> 12;
+    uint4 v;
+    v.x = h;
+    v.y = ~h;
+    v.z = h * 0x297A2D39u + lo;
+    v.w = __funnelshift_l(h, h, 13) ^ hic;
+    return v;
+  }
+};
+
 // ---- 128-bit global accesses, one PTX form per variant ----------------------
 template <int V>
 __device__ __forceinline__ void st128(uint4 *p, const uint4 &v, uint64_t policy) {
@@ -141,7 +170,7 @@ __global__ void __launch_bounds__(kThreads)
     while (tile >= b.s[cur].tile_end) ++cur;
     const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
     const uint64_t rem = b.s[cur].n_vec - v0;
-    const uint32_t seed = b.s[cur].seed;
+    const TilePattern pat(v0, b.s[cur].seed);
     uint4 *p = b.s[cur].base + v0;
     if (rem >= kTileVec) {
 #pragma unroll 1
@@ -149,12 +178,12 @@ __global__ void __launch_bounds__(kThreads)
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const uint32_t j = k + u * kThreads + threadIdx.x;
-          st128<V>(p + j, slice_pattern(v0 + j, seed), policy);
+          st128<V>(p + j, pat.word(j), policy);
         }
       }
     } else {
       for (uint32_t j = threadIdx.x; j < (uint32_t)rem; j += kThreads)
-        st128<V>(p + j, slice_pattern(v0 + j, seed), policy);
+        st128<V>(p + j, pat.word(j), policy);
     }
   }
 }
@@ -177,8 +206,8 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-template <int STAGES>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int STAGES, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1)
     probe_write_bulk_kernel(const __grid_constant__ Batch b, uint32_t sub_vec,
                             uint32_t period_x16) {
   extern __shared__ __align__(128) uint4 ring[];
@@ -191,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
     const uint64_t rem64 = b.s[cur].n_vec - v0;
     const uint32_t rem = rem64 >= kTileVec ? kTileVec : (uint32_t)rem64;
-    const uint32_t seed = b.s[cur].seed;
+    const TilePattern pat(v0, b.s[cur].seed);
     uint4 *buf = ring + (size_t)stage * kTileVec;
     // the bulk store that last read this stage must have drained shared memory
     if (threadIdx.x < nsub)
@@ -199,10 +228,10 @@ __global__ void __launch_bounds__(kThreads, 1)
     __syncthreads();
     if (rem == kTileVec) {
 #pragma unroll 4
-      for (uint32_t j = threadIdx.x; j < kTileVec; j += kThreads)
-        buf[j] = slice_pattern(v0 + j, seed);
+      for (uint32_t j = threadIdx.x; j < kTileVec; j += THREADS)
+        buf[j] = pat.word(j);
     } else {
-      for (uint32_t j = threadIdx.x; j < rem; j += kThreads) buf[j] = slice_pattern(v0 + j, seed);
+      for (uint32_t j = threadIdx.x; j < rem; j += THREADS) buf[j] = pat.word(j);
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
@@ -269,7 +298,7 @@ __global__ void __launch_bounds__(kThreads)
     while (tile >= b.s[cur].tile_end) ++cur;
     const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
     const uint64_t rem = b.s[cur].n_vec - v0;
-    const uint32_t seed = b.s[cur].seed;
+    const TilePattern pat(v0, b.s[cur].seed);
     const uint4 *p = b.s[cur].base + v0;
     if (rem >= kTileVec) {
 #pragma unroll 1
@@ -282,13 +311,13 @@ __global__ void __launch_bounds__(kThreads)
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const uint32_t j = k + u * kThreads + threadIdx.x;
-          any |= differs(got[u], slice_pattern(v0 + j, seed));
+          any |= differs(got[u], pat.word(j));
         }
         if (__any_sync(0xffffffffu, any)) {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
             const uint32_t j = k + u * kThreads + threadIdx.x;
-            const uint4 want = slice_pattern(v0 + j, seed);
+            const uint4 want = pat.word(j);
             report_warp(results + cur, differs(got[u], want), got[u], want, v0 + j);
           }
         }
@@ -299,7 +328,7 @@ __global__ void __launch_bounds__(kThreads)
       for (uint32_t k = 0; k < r; k += kThreads) {
         const uint32_t j = k + threadIdx.x;
         const bool inb = j < r;
-        const uint4 want = slice_pattern(v0 + j, seed);
+        const uint4 want = pat.word(j);
         const uint4 got = inb ? ld128<V>(p + j, policy) : want;
         const bool bad = differs(got, want);
         if (__any_sync(0xffffffffu, bad)) report_warp(results + cur, bad, got, want, v0 + j);
@@ -315,17 +344,19 @@ using WriteFn = void (*)(const Batch);
 using VerifyFn = void (*)(const Batch, DevResult *);
 
 constexpr int kNumWriteVariants = 4;  // STG forms (codes 0..29)
-// Bulk-store codes: 100 + 10 * stages_sel + sub_sel
-//   stages_sel 0 -> 3-stage ring (192 KiB smem), 1 -> 2-stage ring (128 KiB)
-//   sub_sel    0 -> 4 KiB bulk ops, 1 -> 2 KiB, 2 -> 8 KiB, 3 -> 16 KiB, 4 -> 1 KiB
+// Bulk-store codes: 100 * threads_sel + 10 * stages_sel + sub_sel
+//   threads_sel 1 -> 256 threads per CTA, 2 -> 512, 3 -> 1024 (measured: no difference in a
+//               sustained sweep -- the store pass is power-limited there, not fill-limited)
+//   stages_sel  0 -> 3-stage ring (192 KiB smem), 1 -> 2-stage ring (128 KiB)
+//   sub_sel     0 -> 4 KiB bulk ops, 1 -> 2 KiB, 2 -> 8 KiB, 3 -> 16 KiB, 4 -> 1 KiB
 constexpr int kWriteBulkBase = 100;
-constexpr int kDefaultWriteVariant = kWriteBulkBase + 2;  // 3-stage ring, 8 KiB bulk ops
+constexpr int kDefaultWriteVariant = 102;  // 256 threads, 3-stage ring, 8 KiB bulk ops
 // aggregate offered store rate the token buckets add up to (GB/s == bytes/ns)
 constexpr uint32_t kDefaultWriteRateGBps = 7600;
 constexpr uint32_t kBulkSubVec[5] = {256, 128, 512, 1024, 64};
 bool is_bulk_code(int code) {
-  return code >= kWriteBulkBase && (code - kWriteBulkBase) / 10 < 2 &&
-         (code - kWriteBulkBase) % 10 < 5;
+  return code >= kWriteBulkBase && code < 4 * kWriteBulkBase && (code % 100) / 10 < 2 &&
+         code % 10 < 5;
 }
 constexpr int kNumVerifyVariants = 5;
 constexpr int kNumUnrolls = 3;  // U = 2, 4, 8 -> variant index / 10 selects
@@ -393,10 +424,11 @@ struct gs_probe {
   uint64_t pending_bytes = 0;
   bool pending = false;
   int write_variant = kDefaultWriteVariant;
-  bool bulk_attr_set[2] = {false, false};
+  bool bulk_attr_set[6] = {false, false, false, false, false, false};
   uint32_t write_rate_gbps = kDefaultWriteRateGBps;  // 0 = unpaced
-  int verify_variant = 0;  // plain ld.global.v4: best when the pass follows a store pass
-  int ctas_per_sm = 8;     // STG/LDG kernels: CTAs per SM in the grid; 0 = occupancy query
+  int verify_variant = 10;  // U = 2, plain ld.global.v4: 30 registers, 8 CTAs/SM resident;
+                            // best sustained rate after a store pass (tools/probe_sustained_grid.py)
+  int ctas_per_sm = 0;      // STG/LDG kernels: CTAs per SM in the grid; 0 = occupancy query
 };
 
 #define GS_CUDA(call)                                      \
@@ -547,16 +579,23 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
   GS_CUDA(cudaMemsetAsync(p->d_res, 0, sizeof(DevResult) * n, p->stream));
   GS_CUDA(cudaEventRecord(p->ev[0], p->stream));
   if ((passes & GS_PROBE_WRITE) && is_bulk_code(p->write_variant)) {
-    const int stages_sel = (p->write_variant - kWriteBulkBase) / 10;
-    const uint32_t sub_vec = kBulkSubVec[(p->write_variant - kWriteBulkBase) % 10];
+    const int threads_sel = p->write_variant / 100;  // 1, 2, 3
+    const int stages_sel = (p->write_variant % 100) / 10;
+    const uint32_t sub_vec = kBulkSubVec[p->write_variant % 10];
     const int stages = stages_sel == 0 ? 3 : 2;
+    const int threads = 128 << threads_sel;
     const size_t smem = (size_t)stages * kTileVec * sizeof(uint4);
-    void (*fn)(const Batch, uint32_t, uint32_t) =
-        stages == 3 ? probe_write_bulk_kernel<3> : probe_write_bulk_kernel<2>;
-    if (!p->bulk_attr_set[stages_sel]) {
+    using BulkFn = void (*)(const Batch, uint32_t, uint32_t);
+    static const BulkFn kBulkFns[3][2] = {
+        {probe_write_bulk_kernel<3, 256>, probe_write_bulk_kernel<2, 256>},
+        {probe_write_bulk_kernel<3, 512>, probe_write_bulk_kernel<2, 512>},
+        {probe_write_bulk_kernel<3, 1024>, probe_write_bulk_kernel<2, 1024>}};
+    BulkFn fn = kBulkFns[threads_sel - 1][stages_sel];
+    const int slot = (threads_sel - 1) * 2 + stages_sel;
+    if (!p->bulk_attr_set[slot]) {
       GS_CUDA(cudaFuncSetAttribute((const void *)fn,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      p->bulk_attr_set[stages_sel] = true;
+      p->bulk_attr_set[slot] = true;
     }
     // the ring fills an SM's shared memory: exactly one CTA per SM
     const uint64_t grid = tiles < (uint64_t)p->sms ? tiles : (uint64_t)p->sms;
@@ -564,7 +603,7 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
     uint32_t period_x16 = 0;
     if (p->write_rate_gbps)
       period_x16 = (uint32_t)((double)kTileVec * 16.0 * (double)grid / (double)p->write_rate_gbps * 16.0);
-    fn<<<(int)grid, kThreads, smem, p->stream>>>(b, sub_vec, period_x16);
+    fn<<<(int)grid, threads, smem, p->stream>>>(b, sub_vec, period_x16);
     GS_CUDA(cudaGetLastError());
     ++launches;
   } else if (passes & GS_PROBE_WRITE) {

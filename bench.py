@@ -411,7 +411,14 @@ def run_ours(args, rank, world, local_rank):
             "probe": {"batches": int(la[7]), "launches_per_rank": launches_per_rank,
                       "bytes_probed": int(la[1]), "bytes_granted": int(la[2]),
                       "coverage": la[1] / la[2] if la[2] else 0, "grants_dropped": int(la[3]),
-                      "bad_slices": int(la[6])},
+                      "bad_slices": int(la[6]),
+                      "decisions_per_s_if_every_grant_waited_for_its_sweep":
+                          world * TENANTS / ((la[4] + la[5]) / max(la[7], 1) * 1e-3) if live_ms else None,
+                      "note": "grants outrun HBM by design: a wave grants ~%d GiB, one sweep of it takes "
+                              "~%.0f ms, so repeated grants of a range coalesce and coverage is the "
+                              "fraction actually swept; the last line is what the rate would be if "
+                              "Allocate blocked on the sweep (it must not: parity)" % (
+                                  sum(sizes), (la[4] + la[5]) / max(la[7], 1))},
             "list_and_watch": {"devices": int(table.device_count), "payload_bytes": payload,
                                "borrow_segments_ms": law_borrow * 1e3, "encode_copy_ms": law_copy * 1e3,
                                "table_build_ms": law_build * 1e3,

@@ -27,7 +27,7 @@ def oracle_bytes(oracle_lib, nbytes, seed, first=0):
 
 @pytest.mark.parametrize("nbytes", [16, 4096, 64 * 1024, 64 * 1024 + 16, MiB - 16, 3 * MiB + 4080,
                                     37 * MiB])
-@pytest.mark.parametrize("wvariant", [102, 100, 110, 0, 21])
+@pytest.mark.parametrize("wvariant", [302, 202, 102, 100, 110, 314, 0, 21])
 def test_written_pattern_is_bit_exact(probe, oracle_lib, nbytes, wvariant):
     d = probe.alloc(nbytes + 256)
     try:
@@ -64,7 +64,7 @@ def test_verify_counts_match_oracle(probe, oracle_lib, vvariant):
         assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == (mm.value, fb.value, fl.value)
         assert mm.value == 6 and fb.value == 0
     finally:
-        probe.set_variant(verify=0)
+        probe.set_variant(verify=10)
         probe.free(d)
 
 
