@@ -55,3 +55,14 @@ def test_bench_line_contract():
     assert r["value"] > 1000 and r["e2e"]["value"] > 500 and r["gpu_launches"] >= 2
     assert r["roofline"]["bound"] == "hbm" and r["roofline"]["achieved"] > 3000
     assert r["probe"]["bad_slices"] == 0 and "workload" in r["config"]
+
+
+def test_colocation_tool_small_scale():
+    """BASELINE config 4 in miniature on however many GPUs are visible: every tenant allocated,
+    all ranges swept concurrently, the one corrupted tenant (and only it) reported."""
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "colocation.py"), "--scale", "0.01"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-3000:]
+    r = json.loads(out.stdout)
+    assert r["fault_injection"]["flagged_tenants"] == [r["fault_injection"]["victim_tenant"]]
+    assert len(r["probe"]["per_gpu"]) >= 1 and r["allocate"]["decisions"] == len(r["tenants_gib"])
