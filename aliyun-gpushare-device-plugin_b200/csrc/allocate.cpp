@@ -43,14 +43,15 @@ struct Scan {
 
 // Counting ids is a chain of dependent hops (read a length byte, jump): one hop costs an
 // L1 load-to-use latency however little work it is. For a large container the chain is cut
-// into kChains pieces that run interleaved so the loads overlap (measured: 6.8 -> 4.2 ns
-// per id on 2 MB requests; no gain while the request sits in the L2, hence the threshold). A piece starts at a
+// into kChains pieces that run interleaved so the loads overlap (measured on the B200 box's
+// Xeon, tools/exp/scan_bench.cpp: 2.3-2.5 ns per id sequential, 1.3-1.4 ns with four chains
+// and a prefetch, at 1 024 as at 40 960 ids, i.e. 21 -> 38 GB/s of request bytes). A piece starts at a
 // GUESSED record boundary (the first byte after its nominal start that looks like
 // "0x0A <len < 128>" and whose hop lands on another such byte or on the end); the guess
 // is proven, not trusted: the previous piece must land EXACTLY on it. Any surprise (an
 // unknown field, a long length, a miss) makes the caller fall back to the plain
 // sequential walk, so the count is exact for every input.
-constexpr size_t kMultiChainMin = 1u << 20;  // pays off once a container outgrows the L2
+constexpr size_t kMultiChainMin = 4096;
 constexpr int kChains = 4;
 
 inline bool fast_record(const uint8_t *q, const uint8_t *qend) {
