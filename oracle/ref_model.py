@@ -763,9 +763,13 @@ def _fields(buf):
             v = bytes(buf[pos:pos + ln])
             pos += ln
         elif wt == 1:
+            if pos + 8 > len(buf):
+                raise ValueError("truncated fixed64")
             v = bytes(buf[pos:pos + 8])
             pos += 8
         elif wt == 5:
+            if pos + 4 > len(buf):
+                raise ValueError("truncated fixed32")
             v = bytes(buf[pos:pos + 4])
             pos += 4
         else:

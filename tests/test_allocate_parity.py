@@ -201,3 +201,73 @@ def test_multichain_scan_is_exact_on_hostile_ids():
             wire = R._ld(1, inner) + R._ld(1, R._ld(1, b"tail"))
         counts, total = api.request_scan(wire)
         assert counts == [len(ids), 1] and total == len(ids) + 1, trial
+
+
+def test_request_scan_fuzz_agrees_with_oracle_decoder():
+    """Mutated wire bytes: the product either rejects them (GS_E_WIRE) exactly when the oracle's
+    independent protobuf reader does, or counts the same ids per container."""
+    rng = random.Random(4242)
+    base = R.encode_allocate_request([["GPU-aaaa-_-%d" % k for k in range(300)], ["x" * 130, ""], []])
+    agree_ok = agree_bad = 0
+    for trial in range(3000):
+        b = bytearray(base[:rng.choice([len(base), rng.randrange(1, len(base))])])
+        for _ in range(rng.choice([0, 1, 1, 2, 5])):
+            op = rng.random()
+            i = rng.randrange(len(b))
+            if op < 0.5:
+                b[i] = rng.choice([0x0A, 0x00, 0x7F, 0x80, 0xFF, 0x12, 0x0B, 0x0D, 0x09, rng.randrange(256)])
+            elif op < 0.75:
+                del b[i]
+                if not b:
+                    b = bytearray(b"\x0a")
+            else:
+                b.insert(i, rng.randrange(256))
+        wire = bytes(b)
+        try:
+            want = [len(c) for c in _strict_decode(wire)]
+        except ValueError:
+            want = None
+        try:
+            got, total = api.request_scan(wire)
+        except api.L.GpushareError as e:
+            assert e.status == api.L.GS_E_WIRE
+            got = None
+        assert got == want, (trial, wire[:40])
+        agree_ok += want is not None
+        agree_bad += want is None
+    assert agree_ok > 300 and agree_bad > 300          # both outcomes are exercised
+
+
+def _strict_decode(buf):
+    """AllocateRequest -> per-container lists of raw id bytes, raising ValueError on anything a
+    protobuf reader must refuse (truncation, over-long varints, group wire types)."""
+    out = []
+    for f, w, c in R._fields(buf):
+        if f == 1 and w == 2:
+            out.append([v for f2, w2, v in R._fields(c) if f2 == 1 and w2 == 2])
+    return out
+
+
+def test_stateless_allocate_is_thread_safe():
+    """gs_allocate keeps per-thread scratch only: 8 threads deciding different pod lists at once
+    get the answers they would get alone."""
+    import threading
+    table = api.DeviceTable(["GPU-%d" % i for i in range(8)], 16)
+    errors = []
+
+    def worker(t):
+        rng = random.Random(t)
+        pods = [api.Pod("u%d-%d" % (t, k), "default", "p%d" % k, "n", 1 + (k % 5), str((t + k) % 8),
+                        str(rng.randrange(10**6)), "false") for k in range(5 + 9 * t)]
+        for _ in range(200):
+            n = 1 + rng.randrange(5)
+            d = api.allocate(table, "n", R.encode_allocate_request([["i"] * n]), pods, 1)
+            cands = sorted((int(p.ann_assume_time), -i, i) for i, p in enumerate(pods) if p.gpu_mem_limit == n)
+            want = cands[0][2] if cands else -1
+            if len(pods) <= 12 or len({c[0] for c in cands}) == len(cands):
+                if d.pod_index != want:
+                    errors.append((t, n, d.pod_index, want))
+    ts = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+    [t.start() for t in ts]
+    [t.join(60) for t in ts]
+    assert not errors, errors[:3]
