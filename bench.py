@@ -60,10 +60,31 @@ def tenant_sizes_gib(rank):
             return s
 
 
+def _varint(n):
+    out = bytearray()
+    while n >= 0x80:
+        out.append((n & 0x7F) | 0x80)
+        n >>= 7
+    out.append(n)
+    return bytes(out)
+
+
+def encode_allocate_request(containers):
+    """What kubelet sends: AllocateRequest{container_requests=1{devices_ids=1}} (synthetic input;
+    deliberately not taken from oracle/, which only the baseline legs may touch)."""
+    out = bytearray()
+    for ids in containers:
+        inner = bytearray()
+        for i in ids:
+            b = i.encode()
+            inner += b"\x0a" + _varint(len(b)) + b
+        out += b"\x0a" + _varint(len(inner)) + inner
+    return bytes(out)
+
+
 def build_workload(rank, uuid, units):
     """-> (pods as k8s dicts, request wires in arrival order, sizes GiB)."""
     import numpy as np
-    from oracle import ref_model as R
     sizes = tenant_sizes_gib(rank)
     per = 16 if os.environ.get("GS_BENCH_SMALL") else 1024   # units per size step
     rng = np.random.default_rng(SEED + 1000 * rank)
@@ -73,7 +94,7 @@ def build_workload(rank, uuid, units):
         n = gib * per
         ids = ["%s-_-%d" % (uuid, j) for j in free[off:off + n]]
         off += n
-        wires.append(R.encode_allocate_request([ids]))
+        wires.append(encode_allocate_request([ids]))
     pods = []
     for k, gib in enumerate(sizes):
         pods.append({"metadata": {"uid": "tenant-%d-%d" % (rank, k), "name": "tenant-%d" % k,
