@@ -214,7 +214,9 @@ __global__ void __launch_bounds__(THREADS, 1)
   const uint32_t nsub = kTileVec / sub_vec;
   uint32_t cur = 0;
   int stage = 0;
-  uint64_t next_x16 = period_x16 ? global_timer_ns() * 16 : 0;
+  // the bucket's clock is time since kernel start, in 1/16 ns, so it cannot wrap
+  const uint64_t t_start = period_x16 ? global_timer_ns() : 0;
+  uint64_t next_x16 = 0;
   for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
     while (tile >= b.s[cur].tile_end) ++cur;
     const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
@@ -238,7 +240,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     if (threadIdx.x < nsub) {
       if (period_x16) {
         uint64_t now;
-        while ((now = global_timer_ns() * 16) < next_x16) {
+        while ((now = (global_timer_ns() - t_start) * 16) < next_x16) {
         }
         if (now > next_x16 + period_x16) next_x16 = now;  // late: do not burst
         next_x16 += period_x16;

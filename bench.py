@@ -221,6 +221,21 @@ def workload_config(sizes, waves):
             "parallelism": "one process per GPU, no collective"}
 
 
+def host_memcpy_gbps():
+    """Single-thread memcpy of a buffer larger than the L3 (bytes copied / s, reads + writes not
+    double counted): the host-side yardstick for the request scan and the payload copy."""
+    import ctypes
+    n = 256 << 20
+    a, b = ctypes.create_string_buffer(n), ctypes.create_string_buffer(n)
+    ctypes.memmove(b, a, n)
+    best = 0.0
+    for _ in range(3):
+        t0 = time.perf_counter()
+        ctypes.memmove(b, a, n)
+        best = max(best, n / (time.perf_counter() - t0) / 1e9)
+    return best
+
+
 def host_info():
     model = ""
     try:
@@ -446,6 +461,14 @@ def run_ours(args, rank, world, local_rank):
                                "encode_copy_gbps": payload / law_copy / 1e9},
             "clocks": clocks, "host": host_info(),
         }
+        memcpy = host_memcpy_gbps()
+        scan_gbps = (decisions / world) / dt_abi * req_avg / 1e9
+        line["host_roofline"] = {
+            "memcpy_gbps_1_thread": memcpy, "request_bytes_gbps_per_rank": scan_gbps,
+            "frac_of_memcpy": scan_gbps / memcpy,
+            "note": "Allocate is host work: every request byte is touched once by the id scan (one "
+                    "length-prefix hop per ~51-byte id). No GPU roofline applies to it; the yardstick is "
+                    "this box's single-thread memcpy rate."}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(pods_k8s, wires, uuid, units)
         sys.stdout.flush()
