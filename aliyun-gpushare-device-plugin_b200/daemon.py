@@ -63,6 +63,8 @@ def parse_args(argv=None):
     flag("nvml-lib", default="", help="path of libnvidia-ml (tests: the fake NVML)")
     flag("socket-dir", default=os.path.dirname(SERVER_SOCK), help="device-plugins directory")
     boolflag("probe", "sweep each granted slice on the GPU after Allocate")
+    flag("health-probe-interval", type=int, default=0,
+         help="with --probe and --health-check: every N seconds sweep each GPU's free memory (0 = off)")
     boolflag("no-register", "serve without registering with kubelet (harness)")
     a = ap.parse_args(argv)
     for k in ("mps", "health_check", "query_kubelet", "logtostderr", "probe", "no_register"):
@@ -194,6 +196,8 @@ class PluginInstance:
                     self.arenas[d.gpu_index] = sched.probe.alloc(nbytes)
                     sched.grant(self.arenas[d.gpu_index], nbytes, d.pod_index & 0xFFFFFFFF, d.pod_index)
                     sched.pump()
+                    log(self.a.v, 1, "probe: gpu %d, %d bytes granted to pod %d queued for a sweep" % (
+                        d.gpu_index, nbytes, d.pod_index))
             except L.GpushareError as e:
                 log(self.a.v, 1, "probe skipped: %s" % e)
         return d
@@ -212,14 +216,36 @@ class PluginInstance:
                     self.plugin.unhealthy(g)                        # nvidia.go:107-111
 
             def pump():
+                last_sweep = time.time()
                 while not self.stop.is_set():
                     ev = self.nv.health_wait(1000)
                     if ev and not ev[2]:
                         self.plugin.unhealthy(ev[0])
                     for s in self.probes.values():
                         s.pump()
+                    if a.health_probe_interval and time.time() - last_sweep >= a.health_probe_interval:
+                        last_sweep = time.time()
+                        self.health_sweep()
             self.pump_thread = threading.Thread(target=pump, daemon=True)
             self.pump_thread.start()
+
+    def health_sweep(self):
+        """Health-time probe: everything that is free on each GPU right now, minus a margin
+        (tenants' memory is theirs). A mismatch marks the whole GPU unhealthy."""
+        for g, sched in self.probes.items():
+            if sched.inflight is not None:
+                continue                                # an Allocate-time sweep is running
+            try:
+                verdict, tm = sched.probe.sweep_free(margin_bytes=2 << 30)
+            except L.GpushareError as e:
+                log(self.a.v, 1, "health probe skipped on gpu %d: %s" % (g, e))
+                continue
+            if verdict is None:
+                continue
+            log(self.a.v, 1, "health probe: gpu %d swept %d bytes at %.0f GB/s, %d mismatching words" % (
+                g, tm.bytes, tm.gbps(), verdict.mismatches))
+            if not verdict.clean:
+                self.plugin.unhealthy(g)
 
     def Stop(self):
         self.stop.set()

@@ -66,3 +66,51 @@ def test_colocation_tool_small_scale():
     r = json.loads(out.stdout)
     assert r["fault_injection"]["flagged_tenants"] == [r["fault_injection"]["victim_tenant"]]
     assert len(r["probe"]["per_gpu"]) >= 1 and r["allocate"]["decisions"] == len(r["tenants_gib"])
+
+
+def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
+    """The daemon against the real NVML and GPU: enumerate, serve, Allocate for a pod bound to
+    GPU 0, sweep the granted range, and sweep free memory on the health timer."""
+    import signal
+    import time
+
+    import grpc
+
+    from gpushare_b200 import api
+    from gpushare_b200.grpc_harness import KubeletStub
+    with api.Nvml() as nv:
+        uuid = nv.devices()[0].uuid.decode()
+    pods = {"items": [{"metadata": {"uid": "u1", "name": "tenant", "namespace": "default", "annotations": {
+        "ALIYUN_COM_GPU_MEM_IDX": "0", "ALIYUN_COM_GPU_MEM_ASSUME_TIME": "1",
+        "ALIYUN_COM_GPU_MEM_ASSIGNED": "false"}},
+        "spec": {"nodeName": "node-a", "containers": [
+            {"resources": {"limits": {"aliyun.com/gpu-mem": "2"}}}]}, "status": {"phase": "Pending"}}]}
+    (tmp_path / "pods.json").write_text(json.dumps(pods))
+    env = dict(os.environ, NODE_NAME="node-a", PYTHONPATH=ROOT)
+    proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "--v=1", "--memory-unit=GiB",
+                             "--socket-dir", str(tmp_path), "--pod-source-file", str(tmp_path / "pods.json"),
+                             "--no-register", "--probe", "--health-check", "--health-probe-interval=1"],
+                            env=env, stderr=subprocess.PIPE, text=True)
+    try:
+        sock = str(tmp_path / "aliyungpushare.sock")
+        deadline = time.time() + 60
+        while not os.path.exists(sock) and time.time() < deadline:
+            time.sleep(0.1)
+        ch = KubeletStub.connect(sock)
+        grpc.channel_ready_future(ch).result(timeout=30)
+        req = b"\x0a" + bytes([2 * (2 + len(uuid) + 4)]) + b"".join(
+            b"\x0a" + bytes([len(uuid) + 4]) + (uuid + "-_-%d" % j).encode() for j in (1, 2))
+        resp = KubeletStub.method(ch, "Allocate")(req)
+        assert b"ALIYUN_COM_GPU_MEM_IDX" in resp and b"no-gpu-has" not in resp
+        time.sleep(3.5)                                  # let the health timer fire
+        ch.close()
+    finally:
+        proc.send_signal(signal.SIGTERM)
+        try:
+            proc.wait(30)
+        except subprocess.TimeoutExpired:
+            proc.kill()
+    err = proc.stderr.read()
+    assert proc.returncode == 0, err[-2000:]
+    assert "probe: gpu 0, 2147483648 bytes granted to pod 0 queued for a sweep" in err
+    assert "health probe: gpu 0 swept" in err and "0 mismatching words" in err
