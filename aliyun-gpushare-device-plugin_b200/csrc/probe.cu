@@ -241,6 +241,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       if (period_x16) {
         uint64_t now;
         while ((now = (global_timer_ns() - t_start) * 16) < next_x16) {
+          __nanosleep(32);  // park the warp instead of burning issue slots (the board is power-capped)
         }
         if (now > next_x16 + period_x16) next_x16 = now;  // late: do not burst
         next_x16 += period_x16;
@@ -259,6 +260,40 @@ __global__ void __launch_bounds__(THREADS, 1)
     stage = stage + 1 == STAGES ? 0 : stage + 1;
   }
   if (threadIdx.x < nsub) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// ---- paced plain stores --------------------------------------------------------------
+// The same token bucket applied to ordinary STG.128 stores (one CTA per SM, `sub_vec` words
+// per token): pacing, not the TMA engine, is what lifts the store pass off the 6.3 TB/s
+// plateau (tools/exp/stg_paced8.cu: 7.2-7.45 TB/s at 16 KiB per token). No shared memory.
+__global__ void __launch_bounds__(kThreads)
+    probe_write_paced_kernel(const __grid_constant__ Batch b, uint32_t sub_vec, uint32_t period_x16) {
+  uint32_t cur = 0;
+  const uint64_t t_start = period_x16 ? global_timer_ns() : 0;
+  // spread the CTAs' first tokens over one period so they do not all fire together
+  uint64_t next_x16 = (uint64_t)period_x16 * blockIdx.x / gridDim.x;
+  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
+    while (tile >= b.s[cur].tile_end) ++cur;
+    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
+    const uint64_t rem64 = b.s[cur].n_vec - v0;
+    const uint32_t rem = rem64 >= kTileVec ? kTileVec : (uint32_t)rem64;
+    const TilePattern pat(v0, b.s[cur].seed);
+    uint4 *p = b.s[cur].base + v0;
+    for (uint32_t s0 = 0; s0 < rem; s0 += sub_vec) {
+      if (period_x16 && threadIdx.x < 32) {
+        uint64_t now;
+        while ((now = (global_timer_ns() - t_start) * 16) < next_x16) {
+          __nanosleep(32);  // park the warp instead of burning issue slots (the board is power-capped)
+        }
+        if (now > next_x16 + period_x16) next_x16 = now;  // late: do not burst
+        next_x16 += period_x16;
+      }
+      __syncthreads();  // the other warps sleep here until warp 0 holds the token
+      const uint32_t s1 = s0 + sub_vec < rem ? s0 + sub_vec : rem;
+#pragma unroll 4
+      for (uint32_t j = s0 + threadIdx.x; j < s1; j += kThreads) st128<0>(p + j, pat.word(j), 0);
+    }
+  }
 }
 
 // ---- load + compare pass -----------------------------------------------------
@@ -356,6 +391,11 @@ constexpr int kDefaultWriteVariant = 102;  // 256 threads, 3-stage ring, 8 KiB b
 // aggregate offered store rate the token buckets add up to (GB/s == bytes/ns)
 constexpr uint32_t kDefaultWriteRateGBps = 7600;
 constexpr uint32_t kBulkSubVec[5] = {256, 128, 512, 1024, 64};
+// Paced-STG codes: 400 + sub_sel, sub_sel as for the bulk codes (4 KiB, 2, 8, 16, 1) plus
+//   5 -> 32 KiB, 6 -> 64 KiB per token
+constexpr int kWritePacedBase = 400;
+constexpr uint32_t kPacedSubVec[7] = {256, 128, 512, 1024, 64, 2048, 4096};
+bool is_paced_code(int code) { return code >= kWritePacedBase && code < kWritePacedBase + 7; }
 bool is_bulk_code(int code) {
   return code >= kWriteBulkBase && code < 4 * kWriteBulkBase && (code % 100) / 10 < 2 &&
          code % 10 < 5;
@@ -519,7 +559,8 @@ int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
                          int ctas_per_sm) {
   if (!p) return GS_E_INVAL;
   if (write_variant >= 0) {
-    if (!valid_code(write_variant, kNumWriteVariants) && !is_bulk_code(write_variant))
+    if (!valid_code(write_variant, kNumWriteVariants) && !is_bulk_code(write_variant) &&
+        !is_paced_code(write_variant))
       return GS_E_INVAL;
     p->write_variant = write_variant;
   }
@@ -580,7 +621,16 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
   uint32_t launches = 0;
   GS_CUDA(cudaMemsetAsync(p->d_res, 0, sizeof(DevResult) * n, p->stream));
   GS_CUDA(cudaEventRecord(p->ev[0], p->stream));
-  if ((passes & GS_PROBE_WRITE) && is_bulk_code(p->write_variant)) {
+  if ((passes & GS_PROBE_WRITE) && is_paced_code(p->write_variant)) {
+    const uint32_t sub_vec = kPacedSubVec[p->write_variant - kWritePacedBase];
+    const uint64_t grid = tiles < (uint64_t)p->sms ? tiles : (uint64_t)p->sms;
+    uint32_t period_x16 = 0;  // per token of sub_vec words, so that `grid` CTAs offer write_rate_gbps
+    if (p->write_rate_gbps)
+      period_x16 = (uint32_t)((double)sub_vec * 16.0 * (double)grid / (double)p->write_rate_gbps * 16.0);
+    probe_write_paced_kernel<<<(int)grid, kThreads, 0, p->stream>>>(b, sub_vec, period_x16);
+    GS_CUDA(cudaGetLastError());
+    ++launches;
+  } else if ((passes & GS_PROBE_WRITE) && is_bulk_code(p->write_variant)) {
     const int threads_sel = p->write_variant / 100;  // 1, 2, 3
     const int stages_sel = (p->write_variant % 100) / 10;
     const uint32_t sub_vec = kBulkSubVec[p->write_variant % 10];

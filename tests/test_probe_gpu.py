@@ -27,7 +27,7 @@ def oracle_bytes(oracle_lib, nbytes, seed, first=0):
 
 @pytest.mark.parametrize("nbytes", [16, 4096, 64 * 1024, 64 * 1024 + 16, MiB - 16, 3 * MiB + 4080,
                                     37 * MiB])
-@pytest.mark.parametrize("wvariant", [302, 202, 102, 100, 110, 314, 0, 21])
+@pytest.mark.parametrize("wvariant", [302, 202, 102, 100, 110, 314, 403, 400, 406, 0, 21])
 def test_written_pattern_is_bit_exact(probe, oracle_lib, nbytes, wvariant):
     d = probe.alloc(nbytes + 256)
     try:
