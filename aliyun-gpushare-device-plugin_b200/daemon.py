@@ -22,6 +22,7 @@ import ctypes
 import faulthandler
 import json
 import os
+import queue
 import select
 import signal
 import struct
@@ -170,6 +171,8 @@ class PluginInstance:
                         Probe(o), on_bad=lambda tag, v, g=info.nvml_index: self.plugin.unhealthy(g))
         self.unit_bytes = (1 << 20) if unit == api.MiB else (1 << 30)
         self.arenas = {}
+        self.probe_queue = queue.Queue()
+        self.probe_thread = None
         self._allocate = self.plugin.Allocate
         self.plugin.Allocate = self.allocate_and_probe
         self.server = DevicePluginServer(
@@ -180,27 +183,44 @@ class PluginInstance:
         if self.source is not None:
             self.plugin.set_pods(self.source.list())
         d = self._allocate(request)
-        sched = self.probes.get(d.gpu_index)
-        if sched is not None and d.kind == "matched":
-            # exactly the granted range, capped by what is free right now; a failed
-            # allocation never changes the answer (parity)
-            nbytes = d.pod_req_units * self.unit_bytes
+        if d.kind == "matched" and d.gpu_index in self.probes:
+            # the answer is already decided; the sweep is queued for the probe thread and can
+            # neither delay nor change it (parity)
+            self.probe_queue.put((d.gpu_index, d.pod_req_units * self.unit_bytes, d.pod_index))
+        return d
+
+    def probe_worker(self):
+        """Owns every CUDA call of the daemon: sweeps granted ranges as they arrive, harvests
+        verdicts, and runs the health-time sweep on its timer."""
+        last_sweep = time.time()
+        while not self.stop.is_set():
             try:
-                free, _ = sched.probe.mem_info()
-                nbytes = min(nbytes, max(0, free - (1 << 30))) & ~0xFFFFF
-                if nbytes:
-                    old = self.arenas.pop(d.gpu_index, None)
-                    sched.drain()
+                g, nbytes, pod_index = self.probe_queue.get(timeout=0.2)
+            except queue.Empty:
+                g = None
+            if g is not None:
+                sched = self.probes[g]
+                try:
+                    sched.drain()                        # one arena per GPU: finish the previous sweep
+                    old = self.arenas.pop(g, None)
                     if old:
                         sched.probe.free(old)
-                    self.arenas[d.gpu_index] = sched.probe.alloc(nbytes)
-                    sched.grant(self.arenas[d.gpu_index], nbytes, d.pod_index & 0xFFFFFFFF, d.pod_index)
-                    sched.pump()
-                    log(self.a.v, 1, "probe: gpu %d, %d bytes granted to pod %d queued for a sweep" % (
-                        d.gpu_index, nbytes, d.pod_index))
-            except L.GpushareError as e:
-                log(self.a.v, 1, "probe skipped: %s" % e)
-        return d
+                    free, _ = sched.probe.mem_info()
+                    # exactly the granted range, capped by what is free right now
+                    nbytes = min(nbytes, max(0, free - (1 << 30))) & ~0xFFFFF
+                    if nbytes:
+                        self.arenas[g] = sched.probe.alloc(nbytes)
+                        sched.grant(self.arenas[g], nbytes, pod_index & 0xFFFFFFFF, pod_index)
+                        sched.pump()
+                        log(self.a.v, 1, "probe: gpu %d, %d bytes granted to pod %d queued for a sweep" % (
+                            g, nbytes, pod_index))
+                except L.GpushareError as e:
+                    log(self.a.v, 1, "probe skipped: %s" % e)
+            for s in self.probes.values():
+                s.pump()
+            if self.a.health_probe_interval and time.time() - last_sweep >= self.a.health_probe_interval:
+                last_sweep = time.time()
+                self.health_sweep()
 
     def Serve(self):
         a = self.a
@@ -209,6 +229,9 @@ class PluginInstance:
         else:
             self.server.Serve(os.path.join(a.socket_dir, os.path.basename(KUBELET_SOCKET)))
         log(a.v, 1, "Starting to serve on %s" % self.server.socket)
+        if self.probes:
+            self.probe_thread = threading.Thread(target=self.probe_worker, daemon=True)
+            self.probe_thread.start()
         if a.health_check:                                          # server.go:211-229
             bad_mask = self.nv.health_open()
             for g in range(len(self.infos)):
@@ -216,16 +239,10 @@ class PluginInstance:
                     self.plugin.unhealthy(g)                        # nvidia.go:107-111
 
             def pump():
-                last_sweep = time.time()
                 while not self.stop.is_set():
                     ev = self.nv.health_wait(1000)
                     if ev and not ev[2]:
                         self.plugin.unhealthy(ev[0])
-                    for s in self.probes.values():
-                        s.pump()
-                    if a.health_probe_interval and time.time() - last_sweep >= a.health_probe_interval:
-                        last_sweep = time.time()
-                        self.health_sweep()
             self.pump_thread = threading.Thread(target=pump, daemon=True)
             self.pump_thread.start()
 
@@ -233,7 +250,7 @@ class PluginInstance:
         """Health-time probe: everything that is free on each GPU right now, minus a margin
         (tenants' memory is theirs). A mismatch marks the whole GPU unhealthy."""
         for g, sched in self.probes.items():
-            if sched.inflight is not None:
+            if sched.inflight is not None or sched.pending:
                 continue                                # an Allocate-time sweep is running
             try:
                 verdict, tm = sched.probe.sweep_free(margin_bytes=2 << 30)
@@ -253,6 +270,8 @@ class PluginInstance:
         if self.a.health_check:
             self.pump_thread.join(3)
             self.nv.health_close()
+        if self.probe_thread is not None:
+            self.probe_thread.join(10)
         for g, sched in self.probes.items():
             sched.drain()
             if g in self.arenas:

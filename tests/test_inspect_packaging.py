@@ -120,3 +120,66 @@ def test_manifests_keep_the_drop_in_names():
     assert {"patch", "list", "get"} <= rules[("pods",)] and "patch" in rules[("nodes/status",)]
     assert "get" in rules[("nodes", "nodes/proxy")]
     assert kinds["ClusterRoleBinding"]["subjects"][0]["namespace"] == "kube-system"
+
+
+def test_inspect_cli_end_to_end_over_http(tmp_path, monkeypatch, capsys):
+    """main(): kubeconfig -> apiserver (nodes, pods) -> summary / details / single node."""
+    import http.server
+    import json
+    import threading
+    import urllib.parse
+    nodes = NODES + [node("cpu-node", "10.0.0.9", 0, 0)]
+    pods = PODS + [pod("done", "default", "node-a", 3, "0", phase="Succeeded")]
+    seen = []
+
+    class H(http.server.BaseHTTPRequestHandler):
+        def log_message(self, *a):
+            pass
+
+        def do_GET(self):
+            u = urllib.parse.urlsplit(self.path)
+            seen.append(self.path)
+            if u.path == "/api/v1/nodes":
+                doc = {"items": nodes}
+            elif u.path == "/api/v1/nodes/node-a":
+                doc = nodes[0]
+            elif u.path == "/api/v1/pods":
+                sel = urllib.parse.parse_qs(u.query).get("fieldSelector", [""])[0]
+                want = sel.split("=", 1)[1] if sel else None
+                doc = {"items": [p for p in pods if want is None or p["spec"]["nodeName"] == want]}
+            else:
+                self.send_response(404)
+                self.end_headers()
+                return
+            body = json.dumps(doc).encode()
+            self.send_response(200)
+            self.send_header("Content-Length", str(len(body)))
+            self.end_headers()
+            self.wfile.write(body)
+
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), H)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    try:
+        kc = tmp_path / "config"
+        kc.write_text("apiVersion: v1\nkind: Config\ncurrent-context: c\n"
+                      "contexts: [{name: c, context: {cluster: k, user: u}}]\n"
+                      "clusters: [{name: k, cluster: {server: 'http://127.0.0.1:%d'}}]\n"
+                      "users: [{name: u, user: {token: t}}]\n" % srv.server_address[1])
+        monkeypatch.setenv("KUBECONFIG", str(kc))
+        assert I.main([]) == 0
+        out = capsys.readouterr().out
+        assert "GPU Memory(GiB)" in out and "node-a" in out and "cpu-node" not in out   # not a sharing node
+        assert "55/358" in out                                                          # "done" pod filtered
+        assert I.main(["-d", "node-a"]) == 0
+        out = capsys.readouterr().out
+        assert "NAME:       node-a" in out and "train" in out and "elsewhere" not in out
+        assert any("fieldSelector=spec.nodeName%3Dnode-a" in p for p in seen)
+        assert I.main(["--unit", "MiB"]) == 0
+        assert "GPU Memory(MiB)" in capsys.readouterr().out
+    finally:
+        srv.shutdown()
+    monkeypatch.setenv("KUBECONFIG", str(tmp_path / "missing"))
+    monkeypatch.setenv("HOME", str(tmp_path))
+    import pytest
+    with pytest.raises(SystemExit):
+        I.main([])
