@@ -151,6 +151,9 @@ class ProbeScheduler:
     grants arrive faster than HBM can be swept, the newest grants win and the dropped
     ones are counted -- coverage is reported, never faked. A verdict with mismatches is
     handed to `on_bad(tag, verdict)` (the daemon marks the GPU unhealthy there).
+
+    Like the gs_probe underneath, a scheduler serves one caller at a time: own it from one
+    thread (the daemon's probe thread does; Allocate only enqueues work for that thread).
     """
 
     def __init__(self, probe: Probe, on_bad=None, max_pending=L.GS_PROBE_MAX_SLICES):

@@ -184,3 +184,26 @@ def test_health_time_sweep_of_free_memory(probe):
     v, tm = probe.sweep_free(margin_bytes=4 << 30)
     assert v is not None and v.clean
     assert tm.bytes > 100 << 30 and tm.gbps() > 5000       # most of a B200, at HBM speed
+
+
+def test_full_size_properties_40gib(probe):
+    """BASELINE config 4's largest tenant (40 GiB), no oracle needed: a sweep is clean; read back
+    under another seed EVERY word differs and about half of all bits flip (the pattern is a hash);
+    one flipped bit anywhere is found at its exact byte."""
+    nbytes = 40 << 30
+    free, _ = probe.mem_info()
+    if free < nbytes + (2 << 30):
+        pytest.skip("not enough free HBM")
+    d = probe.alloc(nbytes)
+    try:
+        v, tm = probe.run([(d, nbytes, 0xA5A5)])
+        assert v[0].clean and tm.bytes == nbytes
+        w, _ = probe.run([(d, nbytes, 0x5A5A)], L.GS_PROBE_VERIFY)
+        assert w[0].mismatches == nbytes // 16 and w[0].first_bad_byte == 0
+        assert 0.49 < w[0].bit_flips / (nbytes * 8) < 0.51
+        off = (37 << 30) + 4 * 12345
+        probe.inject(d, off, 1 << 9)
+        v, _ = probe.run([(d, nbytes, 0xA5A5)], L.GS_PROBE_VERIFY)
+        assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == (1, off + 1, 1)
+    finally:
+        probe.free(d)
