@@ -83,7 +83,7 @@ int gs_quantity_value(const char *s, size_t len, int64_t *value) {
   }
   // mantissa as an unsigned 128-bit integer with a decimal shift
   unsigned __int128 mant = 0;
-  int digits = 0, nonzero_digits = 0;
+  int digits = 0;
   int exp10 = 0;
   const unsigned __int128 kMantMax = ((unsigned __int128)1 << 120);
   size_t j = i;
@@ -91,7 +91,6 @@ int gs_quantity_value(const char *s, size_t len, int64_t *value) {
     if (mant >= kMantMax / 10) return GS_E_LIMIT;
     mant = mant * 10 + (unsigned)(s[j] - '0');
     ++digits;
-    nonzero_digits += mant != 0;
   }
   if (j < len && s[j] == '.') {
     ++j;
@@ -148,7 +147,6 @@ int gs_quantity_value(const char *s, size_t len, int64_t *value) {
   } else {
     return GS_E_INVAL;
   }
-  (void)nonzero_digits;
   unsigned __int128 v = mant;
   bool inexact = false;
   if (v != 0) {

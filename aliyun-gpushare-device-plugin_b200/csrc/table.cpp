@@ -395,16 +395,14 @@ uint64_t gs_law_generation(const gs_table *t) {
 size_t gs_law_payload_size(const gs_table *t) {
   if (!t) return 0;
   size_t total = 0;
-  const size_t delta = (sizeof(kUnhealthy) - 1) - (sizeof(kHealthy) - 1);
   for (uint32_t g = 0; g < t->n_gpus; ++g) {
     const uint64_t nbad = t->bad_count[g].load(std::memory_order_acquire);
     if (nbad == t->units) {
-      total += t->unhealthy_size[g];  // inner-length varints may widen; use the exact model
+      total += t->unhealthy_size[g];
     } else if (nbad == 0) {
       total += t->healthy_size[g];
     } else {
-      // mixed: exact only if no device's inner length crosses a varint boundary,
-      // which holds for every uuid shorter than 100 chars (inner <= 127 + ...)
+      // mixed: the healthy size plus, per unhealthy device, the exact size difference
       size_t sz = t->healthy_size[g];
       const std::atomic<uint64_t> *w = &t->bad[(size_t)g * t->words_per_gpu];
       const size_t uuid_len = t->uuids[g].size();
@@ -417,7 +415,6 @@ size_t gs_law_payload_size(const gs_table *t) {
           sz += device_wire_size(idl, false) - device_wire_size(idl, true);
         }
       }
-      (void)delta;
       total += sz;
     }
   }
