@@ -210,3 +210,23 @@ def test_c_parse_uint_matches_oracle():
                 api.go_parse_uint(s)
         else:
             assert api.go_parse_uint(s) == want
+
+
+def test_long_uuids_cross_the_one_byte_varint_boundary():
+    """Ids longer than 114 characters make the Device message longer than 127 bytes: two-byte
+    length prefixes in the payload, one-byte ones no longer valid. Still byte-exact."""
+    uuids = ["GPU-" + "x" * 91, "GPU-" + "y" * 60]
+    g = R.Globals("GiB")
+    devs, _ = R.getDevices(g, [(u, 12288) for u in uuids])
+    t = api.DeviceTable.from_raw(uuids, 12288, "GiB")
+    assert t.list_and_watch_bytes() == R.encode_list_and_watch(devs)
+    t.mark_unhealthy_gpu(0)
+    t.mark_unhealthy_device(1, 11)
+    for d in devs[:12] + [devs[23]]:
+        d[1] = "Unhealthy"
+    wire = t.list_and_watch_bytes()
+    assert wire == R.encode_list_and_watch(devs) and len(wire) == t.payload_size()
+    assert t.lookup(uuids[0] + "-_-11") == (0, 11)
+    import pytest
+    with pytest.raises(api.L.GpushareError):
+        api.DeviceTable(["G" * 96], 1)
