@@ -83,25 +83,22 @@ int gs_quantity_value(const char *s, size_t len, int64_t *value) {
   }
   // mantissa as an unsigned 128-bit integer with a decimal shift
   unsigned __int128 mant = 0;
-  int digits = 0;
   int exp10 = 0;
   const unsigned __int128 kMantMax = ((unsigned __int128)1 << 120);
   size_t j = i;
   for (; j < len && (unsigned)(s[j] - '0') <= 9; ++j) {
     if (mant >= kMantMax / 10) return GS_E_LIMIT;
     mant = mant * 10 + (unsigned)(s[j] - '0');
-    ++digits;
   }
   if (j < len && s[j] == '.') {
     ++j;
     for (; j < len && (unsigned)(s[j] - '0') <= 9; ++j) {
       if (mant >= kMantMax / 10) return GS_E_LIMIT;
       mant = mant * 10 + (unsigned)(s[j] - '0');
-      ++digits;
-      --exp10;
+        --exp10;
     }
   }
-  if (digits == 0) return GS_E_INVAL;
+  // no digits at all is accepted: apimachinery's parser turns an empty numerator into "0"
   const char *suf = s + j;
   const size_t sl = len - j;
   int exp2 = 0;

@@ -79,15 +79,13 @@ Quantity parse_quantity(const std::string &s) {
   size_t i = 0;
   bool neg = false;
   if (i < s.size() && (s[i] == '+' || s[i] == '-')) neg = s[i++] == '-';
-  int digits = 0;
-  for (; i < s.size() && s[i] >= '0' && s[i] <= '9'; ++i, ++digits) q.mant = q.mant * 10 + (s[i] - '0');
+  for (; i < s.size() && s[i] >= '0' && s[i] <= '9'; ++i) q.mant = q.mant * 10 + (s[i] - '0');
   if (i < s.size() && s[i] == '.') {
-    for (++i; i < s.size() && s[i] >= '0' && s[i] <= '9'; ++i, ++digits) {
+    for (++i; i < s.size() && s[i] >= '0' && s[i] <= '9'; ++i) {
       q.mant = q.mant * 10 + (s[i] - '0');
       --q.exp10;
     }
   }
-  if (!digits) return q;
   const std::string suf = s.substr(i);
   static const std::map<std::string, int> dec = {{"n", -9}, {"u", -6}, {"m", -3}, {"", 0}, {"k", 3},
                                                  {"M", 6},  {"G", 9},  {"T", 12}, {"P", 15}, {"E", 18}};

@@ -147,8 +147,7 @@ def quantity_value(s) -> int:
             k += 1
         denom = s[j + 1:k]
         j = k
-    if num == "" and denom == "":
-        raise QuantityError(s)
+    # parseQuantityString turns an empty numerator into "0", so ".", "+" and "-" parse as 0
     suffix = s[j:]
     mant = int((num or "0") + denom)
     exp10 = -len(denom)
@@ -157,7 +156,7 @@ def quantity_value(s) -> int:
         exp10 += _DEC_SUFFIX[suffix]
     elif suffix in _BIN_SUFFIX:
         exp2 = _BIN_SUFFIX[suffix]
-    elif suffix[0] in "eE" and len(suffix) > 1:
+    elif len(suffix) > 1 and suffix[0] in "eE":
         body = suffix[1:]
         sign = 1
         if body[0] in "+-":

@@ -71,12 +71,13 @@ def test_go_parse_uint():
                                     ("0", 0), ("1Ki", 1024), ("1.5Gi", 1610612736),
                                     ("2e3", 2000), ("2E3", 2000), ("1E", 10**18),
                                     ("100n", 1), ("-1500m", -2), ("0.5", 1), ("12e-1", 2),
-                                    (".5", 1), ("5.", 5)])
+                                    (".5", 1), ("5.", 5), (".", 0), ("+", 0), ("-", 0), ("E", 0),
+                                    ("Ei", 0), ("1.G", 10**9)])
 def test_quantity_value(s, want):
     assert R.quantity_value(s) == want
 
 
-@pytest.mark.parametrize("s", ["", "abc", "1K", "1ki", "1 Gi", "1e", "e3", "--1", "1Gii"])
+@pytest.mark.parametrize("s", ["", "abc", "1K", "1ki", "1 Gi", "1e", "--1", "1Gii", "1.5.2", "1e+"])
 def test_quantity_value_err(s):
     with pytest.raises(ValueError):
         R.quantity_value(s)

@@ -190,7 +190,8 @@ def test_c_atoi_matches_oracle(s):
                                "1E", "100n", "-1500m", "0.5", "12e-1", ".5", "5.", "", "abc",
                                "1K", "1ki", "1e", "e3", "--1", "1Gii", "9223372036854775807",
                                "9223372036854775808", "8Ei", "7Ei", "1e18", "1e19", "0.000000001",
-                               "123456789012345678901234567890m"])
+                               "123456789012345678901234567890m", ".", "+", "-", "-.", ".m", "+Ki",
+                               "1.G", "1.5.2", "1e+", "++1", "e", "E", "Ei"])
 def test_c_quantity_matches_oracle(s):
     try:
         want = R.quantity_value(s)
