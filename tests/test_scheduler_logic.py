@@ -1,0 +1,73 @@
+"""ProbeScheduler's queueing policy, on CPU with a stand-in engine (the GPU leg is covered by
+tests/test_scheduler_bench_gpu.py)."""
+from gpushare_b200.probe import ProbeScheduler, SliceVerdict, Timing
+
+
+class FakeEngine:
+    def __init__(self):
+        self.busy = False
+        self.submitted = []
+        self.bad_tags = set()
+
+    def submit(self, slices, passes=3):
+        assert not self.busy
+        self.busy = True
+        self.submitted.append(list(slices))
+
+    def idle(self):
+        return not self.busy or self.finish_now
+
+    finish_now = False
+
+    def wait(self):
+        batch = self.submitted[-1]
+        self.busy = False
+        nb = sum(s[1] for s in batch)
+        verdicts = [SliceVerdict(1 if s[3] in self.bad_tags else 0, 0, 1) for s in batch]
+        return verdicts, Timing(1.0, 1.0, nb, 2)
+
+
+def test_grants_coalesce_while_engine_is_busy():
+    e = FakeEngine()
+    s = ProbeScheduler(e)
+    s.grant(0x1000, 64, 1, 0)
+    s.pump()                                  # first batch in flight
+    assert len(e.submitted) == 1 and s.inflight is not None
+    for wave in range(5):                     # the same two ranges granted again and again
+        s.grant(0x1000, 64, 10 + wave, 0)
+        s.grant(0x2000, 32, 20 + wave, 1)
+        s.pump()                              # engine busy: nothing new goes out
+    assert len(e.submitted) == 1 and len(s.pending) == 2 and s.coalesced == 8
+    assert [g[2] for g in s.pending] == [14, 24]          # the newest seed of each range wins
+    e.finish_now = True
+    s.pump()                                  # harvest, then send the two coalesced ranges
+    assert len(e.submitted) == 2 and [g[0] for g in e.submitted[1]] == [0x1000, 0x2000]
+    s.drain()
+    assert s.batches == 2 and s.launches == 4 and s.bytes_probed == 64 + 96
+    assert s.bytes_granted == 64 + 5 * 96 and s.dropped == 0 and s.gbps() > 0
+
+
+def test_queue_overflow_drops_oldest_and_counts():
+    e = FakeEngine()
+    s = ProbeScheduler(e, max_pending=4)
+    s.grant(0, 16, 0, 0)
+    s.pump()
+    for k in range(1, 8):
+        s.grant(0x100 * k, 16, k, k)
+    assert len(s.pending) == 4 and s.dropped == 3
+    assert [g[3] for g in s.pending] == [4, 5, 6, 7]
+    e.finish_now = True
+    s.drain()
+    assert s.bytes_probed == 16 * 5
+
+
+def test_bad_verdicts_reach_the_callback():
+    e = FakeEngine()
+    e.finish_now = True
+    e.bad_tags = {7}
+    seen = []
+    s = ProbeScheduler(e, on_bad=lambda tag, v: seen.append((tag, v.mismatches)))
+    s.grant(0, 16, 0, 3)
+    s.grant(0x100, 16, 0, 7)
+    s.drain()
+    assert seen == [(7, 1)] and s.bad == 1
