@@ -1,0 +1,77 @@
+"""Writes profiles/README.md from the JSON files beside it."""
+import json
+import os
+
+P = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles")
+
+
+def load(name):
+    return json.load(open(os.path.join(P, name)))
+
+
+rows = []
+for n in (1, 2, 4, 8):
+    d = load("r01_bench_%dgpu.json" % n)
+    rows.append((n, d["value"], d["e2e"]["value"], d["roofline"]["achieved"], d["roofline"]["kernels"]["write_gbps"],
+                 d["roofline"]["kernels"]["verify_gbps"], d["roofline"]["alone"]["combined_gbps"]))
+ref = load("r01_bench_reference_1gpu.json")["value"]
+sw = load("r01_allocate_sweep.json")["rows"]
+co = load("r01_colocation_8gpu.json")
+h = load("r01_harness_8gpu.json")
+md = """# profiles/ -- round 1 evidence
+
+All numbers from B200 boxes via `gpurun` (driver 580.159, CUDA 12.9), never under a profiler unless the
+file says ncu. The reference Go binary cannot be built on these machines; "reference model" is
+`oracle/ref_model.cpp`, the reference algorithm restated in C++ with its per-unit costs (conservative).
+Boxes differ a little (host CPU share, GPU sample): the 1-GPU line and the 2/4/8-GPU lines come from
+different calls, so compare within a call.
+
+## Headline: `bench.py`, one process per GPU, MiB granularity (per-GPU shard of BASELINE configs[2]/[3])
+
+| GPUs | decisions/s (C ABI) | decisions/s (public API, e2e) | probe in step, per GPU | store / load | probe alone |
+|---:|---:|---:|---:|---|---:|
+"""
+for n, v, e, a, w, r, al in rows:
+    md += "| %d | %.0f | %.0f | %.0f GB/s (%.0f%% of measured 6538, %.0f%% of nominal 8000) | %.0f / %.0f | %.0f GB/s |\n" % (
+        n, v, e, a, 100 * a / 6538.3, 100 * a / 8000, w, r, al)
+md += """
+Reference model on the 1-GPU call's box, one thread (`r01_bench_reference_1gpu.json`): **%.0f decisions/s**
+=> %.1fx at 1 GPU (e2e / reference).
+
+## Allocate sweep, 8 x B200 worth of ids (1 466 872), single thread both sides (`r01_allocate_sweep.json`)
+
+| ids per request | pods in list | this library /s | reference model /s | ratio | request bytes scanned |
+|---:|---:|---:|---:|---:|---:|
+""" % (ref, rows[0][2] / ref)
+for r in sw:
+    md += "| %d | %d | %.0f | %.0f | %.1fx | %.1f GB/s |\n" % (
+        r["ids"], r["pods"], r["ours_per_s"], r["reference_model_per_s"], r["ratio"], r["ours_request_gbps"])
+pg = co["probe"]["per_gpu"]
+md += """
+## Config 4 co-location (`r01_colocation_8gpu.json`): %s
+
+Every tenant allocated through the C ABI, all granted ranges (%.0f GiB) swept concurrently, one stream per GPU, one
+process: per-GPU combined %.0f-%.0f GB/s, aggregate %.1f TB/s by wall clock; the one corrupted tenant (%d) was the only
+one reported (%s).
+
+## Host-side metrics, 8 GPUs' worth (`r01_harness_8gpu.json`)
+
+* device table build %.0f ms (reference model getDevices %.0f ms); payload %.1f MB
+* ListAndWatch stream open -> last byte at the client: %.0f ms median (Python grpcio)
+* XID -> re-advertised full list at the client, Allocate loop running: p50 %.0f ms, p99 %.0f ms; one re-send per event
+  (the reference design re-sends once per fake device: %d x %.0f ms of marshal each, by arithmetic)
+* Allocate over the unix-socket gRPC harness: %.0f decisions/s at 1 024 ids, %.0f at 40 960 ids
+
+## Kernel evidence
+
+* `r01_bench_launches.md` / `.csv`: ncu launch list of the bench command (store pass ~49.5%%, load pass ~50.5%% of GPU time)
+* `r01_probe_ncu_full.md`: `ncu --set full` of both kernels; DRAM traffic = algorithmic bytes (ratio in `probe_traffic.json`)
+""" % (co["config"], co["probe"]["bytes_swept"] / 2**30, min(p["combined_gbps"] for p in pg),
+       max(p["combined_gbps"] for p in pg), co["probe"]["aggregate_gbps_wall"] / 1000,
+       co["fault_injection"]["victim_tenant"], co["fault_injection"]["flagged_tenants"],
+       h["table_build_ms"], h["reference_model"]["get_devices_ms"], h["payload_bytes"] / 1e6,
+       h["law_open_to_last_byte_ms"]["median"], h["health_readvertise_ms"]["p50"], h["health_readvertise_ms"]["p99"],
+       h["reference_model"]["resends_per_gpu_event_by_design"], h["reference_model"]["marshal_per_send_ms"],
+       h["allocate_over_grpc"]["1024"]["decisions_per_s"], h["allocate_over_grpc"]["40960"]["decisions_per_s"])
+open(os.path.join(P, "README.md"), "w").write(md)
+print(md[:1600])
