@@ -24,6 +24,8 @@ def lib():
         l.ref_add_pod.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int,
                                   C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p),
                                   C.POINTER(C.c_char_p)]
+        l.ref_save_pods.argtypes = [C.c_void_p]
+        l.ref_restore_pods.argtypes = [C.c_void_p]
         l.ref_allocate.restype = C.c_int
         l.ref_allocate.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_int64, C.c_void_p,
                                    C.c_size_t, C.POINTER(C.c_size_t)]
@@ -82,6 +84,13 @@ class RefPlugin:
                                md.get("name", "").encode(),
                                (p.get("spec") or {}).get("nodeName", "").encode(), len(lims), larr,
                                len(ann), keys, vals)
+
+    def save_pods(self):
+        self.l.ref_save_pods(self.h)
+
+    def restore_pods(self):
+        """Re-install the saved lister answer without going through Python marshalling."""
+        self.l.ref_restore_pods(self.h)
 
     def allocate(self, wire: bytes, now=0):
         """-> (kind string, response bytes, patched pod index or -1)."""

@@ -32,6 +32,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <time.h>
 
 #include <algorithm>
 #include <map>
@@ -337,6 +338,7 @@ struct RefPlugin {
   bool disableCGPUIsolation = false;
   std::mutex mu;
   std::vector<Pod> podList;  // what the lister returns (podmanager.go:187-245)
+  std::vector<Pod> savedList;  // a fresh copy of the lister's answer, for benchmarks
   std::vector<uint8_t> scratch;
   int last_patched = -1;
   std::string last_patch;
@@ -582,6 +584,27 @@ REF_EXPORT void ref_add_pod(void *h, const char *uid, const char *ns, const char
   for (int i = 0; i < n_ann; ++i) pod.d->annotations[keys[i]] = vals[i];
   p->podList.push_back(pod);
 }
+// Benchmarks re-install the same lister answer before every wave; doing that from Python would
+// charge the reference arm for ctypes marshalling it does not owe. save/restore keep it in C++:
+// restore deep-copies the saved pods (a fresh LIST result shares nothing with the last one).
+REF_EXPORT void ref_save_pods(void *h) {
+  RefPlugin *p = (RefPlugin *)h;
+  p->savedList.clear();
+  for (const Pod &pod : p->podList) {
+    Pod c = pod;
+    c.d = std::make_shared<PodData>(*pod.d);
+    p->savedList.push_back(c);
+  }
+}
+REF_EXPORT void ref_restore_pods(void *h) {
+  RefPlugin *p = (RefPlugin *)h;
+  p->podList.clear();
+  for (const Pod &pod : p->savedList) {
+    Pod c = pod;
+    c.d = std::make_shared<PodData>(*pod.d);
+    p->podList.push_back(c);
+  }
+}
 REF_EXPORT int ref_allocate(void *h, const uint8_t *req, size_t len, int64_t now, uint8_t *resp,
                             size_t cap, size_t *resp_len) {
   RefPlugin *p = (RefPlugin *)h;
@@ -605,4 +628,28 @@ REF_EXPORT size_t ref_list_and_watch(void *h, uint8_t *buf, size_t cap) {
 REF_EXPORT void ref_mark_unhealthy(void *h, uint64_t dev_index) {  // server.go:189
   RefPlugin *p = (RefPlugin *)h;
   if (dev_index < p->devs.size()) p->devs[dev_index]->Health = "Unhealthy";
+}
+
+// The same loop for the reference model (see oracle/driver.c).
+REF_EXPORT double ref_drive_rounds(void *h, const uint8_t *wire, size_t len, int per_round, double budget_s,
+                                   uint64_t *failed) {
+  RefPlugin *p = (RefPlugin *)h;
+  uint64_t done = 0, bad = 0;
+  auto now = [] {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+  };
+  const double t0 = now();
+  double t = t0;
+  while (t - t0 < budget_s) {
+    ref_restore_pods(h);
+    for (int k = 0; k < per_round; ++k) {
+      if (p->Allocate(wire, len, 1, p->scratch) != 0) ++bad;
+      ++done;
+    }
+    t = now();
+  }
+  if (failed) *failed = bad;
+  return (double)done / (t - t0);
 }

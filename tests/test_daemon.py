@@ -9,7 +9,6 @@ import tempfile
 import time
 
 import grpc
-import pytest
 
 from gpushare_b200 import daemon
 from gpushare_b200.grpc_harness import KubeletStub

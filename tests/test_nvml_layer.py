@@ -1,6 +1,5 @@
 """NVML layer against the fake libnvidia-ml (BASELINE configs 1 and 5)."""
 import ctypes as C
-import os
 import threading
 import time
 

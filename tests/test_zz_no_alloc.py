@@ -11,7 +11,6 @@ must not see anything the first left in the shared array.
 
 Collected last on purpose (conftest keeps test_zz_* at the end).
 """
-import ctypes as C
 
 import pytest
 

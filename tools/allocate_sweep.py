@@ -24,6 +24,7 @@ uuids = ["GPU-%08x-0000-0000-0000-%012x" % (i, i) for i in range(GPUS)]
 rng = random.Random(20261106)
 table = api.DeviceTable(uuids, UNITS, api.MiB)
 lib = L.load()
+drv = C.CDLL(os.path.join(ROOT, "oracle", "libgs_oracle.so"))   # C timing loops (oracle/driver.c)
 rows = []
 for n in (1024, 4096, 16384, 40960):
     pool = rng.sample(range(GPUS * UNITS), n)
@@ -46,29 +47,21 @@ for n in (1024, 4096, 16384, 40960):
         rbuf = C.create_string_buffer(1 << 16)
         rn = C.c_size_t()
 
-        def ours_round():
-            lib.gs_plugin_set_pods(plug.h, plist.views, plist.n)
-            for _ in range(npods):
-                rc = lib.gs_plugin_allocate(plug.h, wire, len(wire), resp, 4096, C.byref(res))
-                assert rc == 0 and res.kind == 0
-
-        def ref_round():
-            ref.set_pods_k8s(k8s)
-            for _ in range(npods):
-                assert ref.l.ref_allocate(ref.h, wire, len(wire), 1, rbuf, len(rbuf), C.byref(rn)) == 0
-
-        def rate(fn, budget):
-            fn()
-            t0, rounds = time.perf_counter(), 0
-            while time.perf_counter() - t0 < budget:
-                fn()
-                rounds += 1
-            return rounds * npods / (time.perf_counter() - t0)
-
-        o, r = rate(ours_round, 0.6), rate(ref_round, 0.8)
+        failed = C.c_uint64()
+        drv.gs_drive_rounds.restype = C.c_double
+        o = drv.gs_drive_rounds(C.cast(lib.gs_plugin_set_pods, C.c_void_p), C.cast(lib.gs_plugin_allocate, C.c_void_p),
+                                plug.h, plist.views, C.c_size_t(plist.n), wire, C.c_size_t(len(wire)), npods,
+                                C.c_double(0.6), C.byref(failed))
+        assert failed.value == 0, failed.value
+        ref.set_pods_k8s(k8s)
+        ref.save_pods()
+        drv.ref_drive_rounds.restype = C.c_double
+        r = drv.ref_drive_rounds(C.c_void_p(ref.h), wire, C.c_size_t(len(wire)), npods, C.c_double(0.8),
+                                 C.byref(failed))
+        assert failed.value == 0, failed.value
         # same answers on both sides for this workload
         lib.gs_plugin_set_pods(plug.h, plist.views, plist.n)
-        ref.set_pods_k8s(k8s)
+        ref.restore_pods()
         lib.gs_plugin_allocate(plug.h, wire, len(wire), resp, 4096, C.byref(res))
         kind, rresp, rp = ref.allocate(wire, 1)
         assert R.decode_allocate_response(C.string_at(resp, res.resp_len)) == R.decode_allocate_response(rresp)
@@ -78,4 +71,6 @@ for n in (1024, 4096, 16384, 40960):
         print("ids %6d pods %2d: ours %9.0f/s  ref %8.0f/s  x%.1f  (scan %.1f GB/s)" % (
             n, npods, o, r, o / r, o * len(wire) / 1e9), file=sys.stderr, flush=True)
 print(json.dumps({"config": "BASELINE configs[2]: 8 x B200, MiB units, %d fake ids" % (GPUS * UNITS),
-                  "host": {"nproc": os.cpu_count()}, "threads": 1, "rows": rows}, indent=1))
+                  "host": {"nproc": os.cpu_count()}, "threads": 1,
+                  "timing": "C loops on both sides (oracle/driver.c, ref_drive_rounds): no interpreter in the timed region",
+                  "rows": rows}, indent=1))
