@@ -207,3 +207,25 @@ def test_full_size_properties_40gib(probe):
         assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == (1, off + 1, 1)
     finally:
         probe.free(d)
+
+
+@pytest.mark.parametrize("wvariant", [102, 302, 110, 202, 403, 400, 406, 0, 21])
+@pytest.mark.parametrize("nbytes", [16, 48, 64 * 1024 - 16, 64 * 1024 + 16, 5 * 64 * 1024 + 4096 + 16])
+def test_store_pass_stays_inside_the_granted_range(probe, wvariant, nbytes):
+    """Bounds check of our own (compute-sanitizer is closed on this pool): guard bands written
+    with one seed on both sides of a slice must read back clean after the slice itself is swept
+    with every store form, whatever the slice's raggedness."""
+    guard = 8192
+    d = probe.alloc(2 * guard + nbytes + 256)
+    try:
+        left, mid, right = (d, guard, 0xAAAA), (d + guard, nbytes, 0x1234), (d + guard + nbytes, guard, 0xBBBB)
+        probe.set_variant(write=102)
+        probe.run([left, right], L.GS_PROBE_WRITE)
+        probe.set_variant(write=wvariant)
+        v, _ = probe.run([mid])
+        assert v[0].clean
+        g, _ = probe.run([left, right], L.GS_PROBE_VERIFY)
+        assert g[0].clean and g[1].clean, (wvariant, nbytes, g)
+    finally:
+        probe.set_variant(write=102)
+        probe.free(d)
