@@ -62,6 +62,9 @@ one reported (%s).
   (the reference design re-sends once per fake device: %d x %.0f ms of marshal each, by arithmetic)
 * Allocate over the unix-socket gRPC harness: %.0f decisions/s at 1 024 ids, %.0f at 40 960 ids
 
+| GPUs' worth of ids | payload | table build | ListAndWatch open -> last byte (median) | XID -> re-advertised list p50 / p99 | Allocate over gRPC, 1 024 ids |
+|---:|---:|---:|---:|---:|---:|
+%s
 ## Kernel evidence
 
 * `r01_bench_launches.md` / `.csv`: ncu launch list of the bench command (store pass ~49.5%%, load pass ~50.5%% of GPU time)
@@ -72,6 +75,11 @@ one reported (%s).
        h["table_build_ms"], h["reference_model"]["get_devices_ms"], h["payload_bytes"] / 1e6,
        h["law_open_to_last_byte_ms"]["median"], h["health_readvertise_ms"]["p50"], h["health_readvertise_ms"]["p99"],
        h["reference_model"]["resends_per_gpu_event_by_design"], h["reference_model"]["marshal_per_send_ms"],
-       h["allocate_over_grpc"]["1024"]["decisions_per_s"], h["allocate_over_grpc"]["40960"]["decisions_per_s"])
+       h["allocate_over_grpc"]["1024"]["decisions_per_s"], h["allocate_over_grpc"]["40960"]["decisions_per_s"],
+       "".join("| %d | %.1f MB | %.1f ms | %.0f ms | %.0f / %.0f ms | %.0f /s |\n" % (
+           n, x["payload_bytes"] / 1e6, x["table_build_ms"], x["law_open_to_last_byte_ms"]["median"],
+           x["health_readvertise_ms"]["p50"], x["health_readvertise_ms"]["p99"],
+           x["allocate_over_grpc"]["1024"]["decisions_per_s"])
+           for n, x in ((n, load("r01_harness_%dgpu.json" % n)) for n in (1, 2, 4, 8))))
 open(os.path.join(P, "README.md"), "w").write(md)
 print(md[:1600])
