@@ -221,7 +221,8 @@ def workload_config(sizes, waves):
                         "list, requests of n*1024 ids; probe of each granted range" % sizes,
             "waves_per_step": waves, "decisions_per_step": waves * TENANTS,
             "request_bytes_avg": None, "l2": "probed ranges (>= 100 GiB per batch) exceed the 126 MB L2",
-            "parallelism": "one process per GPU, no collective"}
+            "parallelism": "one process per GPU, no collective; each rank decides for its own GPU's shard of the "
+                           "node (one kubelet queue feeding one plugin would run at the 1-GPU rate)"}
 
 
 def host_memcpy_gbps():
