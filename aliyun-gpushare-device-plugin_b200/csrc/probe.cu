@@ -206,11 +206,13 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-template <int STAGES, int THREADS>
+template <int STAGES, int THREADS, bool HINT = false>
 __global__ void __launch_bounds__(THREADS, 1)
     probe_write_bulk_kernel(const __grid_constant__ Batch b, uint32_t sub_vec,
                             uint32_t period_x16) {
   extern __shared__ __align__(128) uint4 ring[];
+  uint64_t policy = 0;
+  if constexpr (HINT) policy = evict_first_policy();
   const uint32_t nsub = kTileVec / sub_vec;
   uint32_t cur = 0;
   int stage = 0;
@@ -250,10 +252,17 @@ __global__ void __launch_bounds__(THREADS, 1)
       if (first < rem) {
         const uint32_t cnt = rem - first < sub_vec ? rem - first : sub_vec;
         const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf + first);
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
-                         b.s[cur].base + v0 + first),
-                     "r"(saddr), "r"(cnt * 16u)
-                     : "memory");
+        if constexpr (HINT)
+          asm volatile(
+              "cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(
+                  b.s[cur].base + v0 + first),
+              "r"(saddr), "r"(cnt * 16u), "l"(policy)
+              : "memory");
+        else
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                           b.s[cur].base + v0 + first),
+                       "r"(saddr), "r"(cnt * 16u)
+                       : "memory");
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     }
@@ -384,7 +393,8 @@ constexpr int kNumWriteVariants = 4;  // STG forms (codes 0..29)
 // Bulk-store codes: 100 * threads_sel + 10 * stages_sel + sub_sel
 //   threads_sel 1 -> 256 threads per CTA, 2 -> 512, 3 -> 1024 (measured: no difference in a
 //               sustained sweep -- the store pass is power-limited there, not fill-limited)
-//   stages_sel  0 -> 3-stage ring (192 KiB smem), 1 -> 2-stage ring (128 KiB)
+//   stages_sel  0 -> 3-stage ring (192 KiB smem), 1 -> 2-stage ring (128 KiB),
+//               2 -> 3-stage ring with an L2 evict-first hint on the bulk stores
 //   sub_sel     0 -> 4 KiB bulk ops, 1 -> 2 KiB, 2 -> 8 KiB, 3 -> 16 KiB, 4 -> 1 KiB
 constexpr int kWriteBulkBase = 100;
 constexpr int kDefaultWriteVariant = 102;  // 256 threads, 3-stage ring, 8 KiB bulk ops
@@ -397,7 +407,7 @@ constexpr int kWritePacedBase = 400;
 constexpr uint32_t kPacedSubVec[7] = {256, 128, 512, 1024, 64, 2048, 4096};
 bool is_paced_code(int code) { return code >= kWritePacedBase && code < kWritePacedBase + 7; }
 bool is_bulk_code(int code) {
-  return code >= kWriteBulkBase && code < 4 * kWriteBulkBase && (code % 100) / 10 < 2 &&
+  return code >= kWriteBulkBase && code < 4 * kWriteBulkBase && (code % 100) / 10 < 3 &&
          code % 10 < 5;
 }
 constexpr int kNumVerifyVariants = 5;
@@ -466,7 +476,7 @@ struct gs_probe {
   uint64_t pending_bytes = 0;
   bool pending = false;
   int write_variant = kDefaultWriteVariant;
-  bool bulk_attr_set[6] = {false, false, false, false, false, false};
+  bool bulk_attr_set[9] = {false, false, false, false, false, false, false, false, false};
   uint32_t write_rate_gbps = kDefaultWriteRateGBps;  // 0 = unpaced
   int verify_variant = 10;  // U = 2, plain ld.global.v4: 30 registers, 8 CTAs/SM resident;
                             // best sustained rate after a store pass (tools/probe_sustained_grid.py)
@@ -634,16 +644,19 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
     const int threads_sel = p->write_variant / 100;  // 1, 2, 3
     const int stages_sel = (p->write_variant % 100) / 10;
     const uint32_t sub_vec = kBulkSubVec[p->write_variant % 10];
-    const int stages = stages_sel == 0 ? 3 : 2;
+    const int stages = stages_sel == 1 ? 2 : 3;
     const int threads = 128 << threads_sel;
     const size_t smem = (size_t)stages * kTileVec * sizeof(uint4);
     using BulkFn = void (*)(const Batch, uint32_t, uint32_t);
-    static const BulkFn kBulkFns[3][2] = {
-        {probe_write_bulk_kernel<3, 256>, probe_write_bulk_kernel<2, 256>},
-        {probe_write_bulk_kernel<3, 512>, probe_write_bulk_kernel<2, 512>},
-        {probe_write_bulk_kernel<3, 1024>, probe_write_bulk_kernel<2, 1024>}};
+    static const BulkFn kBulkFns[3][3] = {
+        {probe_write_bulk_kernel<3, 256>, probe_write_bulk_kernel<2, 256>,
+         probe_write_bulk_kernel<3, 256, true>},
+        {probe_write_bulk_kernel<3, 512>, probe_write_bulk_kernel<2, 512>,
+         probe_write_bulk_kernel<3, 512, true>},
+        {probe_write_bulk_kernel<3, 1024>, probe_write_bulk_kernel<2, 1024>,
+         probe_write_bulk_kernel<3, 1024, true>}};
     BulkFn fn = kBulkFns[threads_sel - 1][stages_sel];
-    const int slot = (threads_sel - 1) * 2 + stages_sel;
+    const int slot = (threads_sel - 1) * 3 + stages_sel;
     if (!p->bulk_attr_set[slot]) {
       GS_CUDA(cudaFuncSetAttribute((const void *)fn,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

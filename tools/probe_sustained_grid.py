@@ -18,8 +18,8 @@ with Probe(0) as p:
     sl = [(d + k * per, per, 5 + k) for k in range(nslices)]
     for _ in range(3):
         p.run(sl)
-    for wcode, rate in ((403, 7500), (403, 7600), (403, 7400), (402, 7500), (400, 7500), (405, 7500), (406, 7300), (102, 7600), (403, 0)):
-        for v in (10,):
+    for wcode, rate in ((102, 7600), (122, 7600), (102, 7600), (122, 7600)):
+        for v in (10, 13, 11):
             for ctas in (0,):
                 p.set_variant(write=wcode, verify=v, ctas_per_sm=ctas)
                 p.set_write_rate(rate)
