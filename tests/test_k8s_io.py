@@ -211,3 +211,18 @@ users: [{name: u, user: {token: abc}}]
     monkeypatch.delenv("KUBERNETES_SERVICE_HOST", raising=False)
     with pytest.raises(RuntimeError, match="in-cluster"):
         k8s_io.ApiConfig.load()
+
+
+def test_podgetter_prints_kubelet_pods(capsys):
+    from gpushare_b200 import podgetter
+    cluster = FakeCluster(PODS)
+    _Handler.cluster, _Handler.log = cluster, []
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), _Handler)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    try:
+        assert podgetter.main(["--token", "abc", "--kubelet-url", "http://127.0.0.1:%d" % srv.server_address[1]]) == 0
+    finally:
+        srv.shutdown()
+    out = json.loads(capsys.readouterr().out)
+    assert [p["metadata"]["name"] for p in out["items"]] == ["a", "b", "run", "other", "big"]
+    assert _Handler.log[0][3] == "Bearer abc"
