@@ -40,7 +40,10 @@ int64_t real_now_ns() {
   return (int64_t)ts.tv_sec * 1000000000ll + ts.tv_nsec;
 }
 
-std::string to_string(const gs_str &s) { return s.p ? std::string(s.p, s.n) : std::string(); }
+void assign(std::string &dst, const gs_str &s) {
+  if (s.p) dst.assign(s.p, s.n);
+  else dst.clear();
+}
 gs_str view(const std::string &s) { return gs_str{s.data(), s.size()}; }
 
 }  // namespace
@@ -97,25 +100,26 @@ void gs_plugin_free(gs_plugin *p) {
 int gs_plugin_set_pods(gs_plugin *p, const gs_pod_view *pods, size_t n) {
   if (!p || (!pods && n)) return GS_E_INVAL;
   std::lock_guard<std::mutex> lk(p->mu);
-  p->pods.clear();
+  // slots and their strings are reused: re-installing a list of the same shape (every
+  // lister refresh) allocates nothing
   p->pods.resize(n);
-  p->views.assign(n, gs_pod_view{});
+  p->views.resize(n);
   for (size_t i = 0; i < n; ++i) {
     StoredPod &s = p->pods[i];
-    s.uid = to_string(pods[i].uid);
-    s.ns = to_string(pods[i].ns);
-    s.name = to_string(pods[i].name);
-    s.node = to_string(pods[i].node_name);
+    assign(s.uid, pods[i].uid);
+    assign(s.ns, pods[i].ns);
+    assign(s.name, pods[i].name);
+    assign(s.node, pods[i].node_name);
     s.limit = pods[i].gpu_mem_limit;
     s.has_idx = pods[i].ann_idx.p != nullptr;
     s.has_time = pods[i].ann_assume_time.p != nullptr;
     s.has_assigned = pods[i].ann_assigned.p != nullptr;
-    s.idx = to_string(pods[i].ann_idx);
-    s.time = to_string(pods[i].ann_assume_time);
-    s.assigned = to_string(pods[i].ann_assigned);
+    assign(s.idx, pods[i].ann_idx);
     // room for "true" and a 20-digit timestamp so the patch is applied in place
-    s.time.reserve(32);
-    s.assigned.reserve(16);
+    if (s.time.capacity() < 32) s.time.reserve(32);
+    if (s.assigned.capacity() < 16) s.assigned.reserve(16);
+    assign(s.time, pods[i].ann_assume_time);
+    assign(s.assigned, pods[i].ann_assigned);
   }
   for (size_t i = 0; i < n; ++i) p->refresh_view(i);
   return GS_OK;

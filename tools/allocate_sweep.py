@@ -26,7 +26,7 @@ table = api.DeviceTable(uuids, UNITS, api.MiB)
 lib = L.load()
 drv = C.CDLL(os.path.join(ROOT, "oracle", "libgs_oracle.so"))   # C timing loops (oracle/driver.c)
 rows = []
-for n in (1024, 4096, 16384, 40960):
+for n in (2, 1024, 4096, 16384, 40960):      # 2 = the GiB-unit binpack-1 request of configs[0]/[1]
     pool = rng.sample(range(GPUS * UNITS), n)
     wire = R.encode_allocate_request([["%s-_-%d" % (uuids[x // UNITS], x % UNITS) for x in pool]])
     for npods in (1, 8, 64):
