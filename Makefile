@@ -45,4 +45,10 @@ $(FAKE_NVML): tests/fake_nvml/fake_nvml.c
 clean:
 	rm -f $(OBJS) $(CORE_SO) $(ORACLE_OBJS) $(ORACLE_SO) $(FAKE_NVML)
 
-.PHONY: all clean
+test: all
+	python -m pytest tests -q -m "not gpu"
+
+test-gpu: all
+	python -m pytest tests -q -m gpu
+
+.PHONY: all clean test test-gpu
