@@ -353,7 +353,16 @@ GS_API int gs_probe_inject(gs_probe *p, void *base, uint64_t byte_offset,
                            uint32_t mask);
 /* Copy helpers so tests need no other CUDA binding. */
 GS_API int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t bytes);
-/* Kernel variant selection for tuning; -1 keeps the default. */
+/* Kernel variant selection for tuning; -1 keeps the default.
+ *   write_variant  100*T + 10*S + B : bulk async stores (default 102). T = 1/2/3 -> 256/512/1024
+ *                  threads; S = 0/1/2 -> 3-stage ring / 2-stage / 3-stage + L2 evict-first hint;
+ *                  B = 0..4 -> 4/2/8/16/1 KiB per bulk op
+ *                  400 + B : paced plain STG.128, B = 0..6 -> 4/2/8/16/1/32/64 KiB per token
+ *                  10*U + F : unpaced STG.128, U = 0/1/2 -> unroll 4/2/8, F = 0..3 -> plain/.cs/
+ *                  L1::no_allocate/L2 evict-first
+ *   verify_variant 10*U + F (default 10): U as above; F = 0..4 -> plain/nc+L1::no_allocate/.cs/
+ *                  nc+L2 evict-first/nc+L2::256B prefetch
+ *   ctas_per_sm    grid size of the STG/LDG kernels in CTAs per SM; 0 = resident CTAs (default) */
 GS_API int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
                                 int ctas_per_sm);
 /* Offered rate (GB/s, whole GPU) the store pass paces itself to; 0 = unpaced.
