@@ -243,7 +243,19 @@ class DeviceTable:
         return self.lib.gs_law_payload_size(self.h)
 
     def list_and_watch_bytes(self):
-        """The serialized v1beta1.ListAndWatchResponse (one copy into a Python bytes)."""
+        """The serialized v1beta1.ListAndWatchResponse as Python bytes. The bytes object is kept
+        per health generation: a second stream (kubelet restart) or a second subscriber gets
+        the same object without another 90 MB copy."""
+        gen = self.generation
+        cached = getattr(self, "_law_cache", None)
+        if cached is not None and cached[0] == gen:
+            return cached[1]
+        out = self._encode_law()
+        if self.generation == gen:           # no health change raced with the encode
+            self._law_cache = (gen, out)
+        return out
+
+    def _encode_law(self):
         n = self.payload_size()
         buf = C.create_string_buffer(max(n, 1))
         out = C.c_size_t()
