@@ -16,7 +16,7 @@ GS_UNIT_GIB, GS_UNIT_MIB = 0, 1
 GS_ALL_GPUS = -1
 GS_UUID_MAX = 96
 GS_PROBE_MAX_SLICES = 64
-GS_PROBE_WRITE, GS_PROBE_VERIFY = 1, 2
+GS_PROBE_WRITE, GS_PROBE_VERIFY, GS_PROBE_SCRUB = 1, 2, 4
 (GS_ALLOC_MATCHED, GS_ALLOC_SINGLE_GPU, GS_ALLOC_ERR_NO_MATCH, GS_ALLOC_ERR_BAD_INDEX,
  GS_ALLOC_ERR_PODS, GS_ALLOC_ERR_PATCH) = range(6)
 
@@ -68,7 +68,7 @@ class SliceResult(C.Structure):
 
 class ProbeTiming(C.Structure):
     _fields_ = [("write_ms", C.c_float), ("verify_ms", C.c_float), ("bytes", C.c_uint64),
-                ("launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("launches", C.c_uint32), ("scrub_ms", C.c_float)]
 
 
 _P = C.POINTER

@@ -385,6 +385,26 @@ __global__ void __launch_bounds__(kThreads)
 
 __global__ void probe_inject_kernel(uint32_t *word, uint32_t mask) { *word ^= mask; }
 
+// ---- L2 scrub ------------------------------------------------------------------------
+// Between the passes (GS_PROBE_SCRUB): stream a buffer larger than the L2 through it, so the
+// store pass's dirty lines are written back and the slice's lines are displaced. The load
+// pass then comes from DRAM even when the slice is smaller than the L2, and no longer has
+// the write-back running underneath it.
+constexpr uint64_t kScrubBytes = 192ull << 20;  // L2 is 126 MB
+__global__ void __launch_bounds__(kThreads)
+    probe_scrub_kernel(const uint4 *__restrict__ buf, uint64_t n_vec, uint32_t *sink) {
+  const uint64_t stride = (uint64_t)gridDim.x * kThreads;
+  uint32_t acc = 0;
+  uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
+  for (; i + 3 * stride < n_vec; i += 4 * stride) {
+    const uint4 a = ld128<0>(buf + i, 0), b = ld128<0>(buf + i + stride, 0);
+    const uint4 c = ld128<0>(buf + i + 2 * stride, 0), d = ld128<0>(buf + i + 3 * stride, 0);
+    acc ^= a.x ^ a.w ^ b.x ^ b.w ^ c.x ^ c.w ^ d.x ^ d.w;
+  }
+  for (; i < n_vec; i += stride) acc ^= ld128<0>(buf + i, 0).x;
+  if (acc == 0x9E3779B9u) *sink = acc;  // the buffer is zero-filled: never taken, keeps the loads
+}
+
 // ---- variant dispatch ----------------------------------------------------------
 using WriteFn = void (*)(const Batch);
 using VerifyFn = void (*)(const Batch, DevResult *);
@@ -467,7 +487,8 @@ struct gs_probe {
   int dev = 0;
   int sms = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  void *scrub = nullptr;  // kScrubBytes, allocated on the first GS_PROBE_SCRUB
   DevResult *d_res = nullptr;
   DevResult *h_res = nullptr;  // pinned
   uint32_t pending_n = 0;
@@ -510,7 +531,7 @@ int gs_probe_open(int cuda_ordinal, gs_probe **out) {
   p->dev = cuda_ordinal;
   cudaError_t e = cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, cuda_ordinal);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking);
-  for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
+  for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
   if (e == cudaSuccess) e = cudaMalloc(&p->d_res, sizeof(DevResult) * GS_PROBE_MAX_SLICES);
   if (e == cudaSuccess) e = cudaMallocHost(&p->h_res, sizeof(DevResult) * GS_PROBE_MAX_SLICES);
   if (e != cudaSuccess) {
@@ -527,6 +548,7 @@ int gs_probe_close(gs_probe *p) {
   DeviceGuard g(p->dev);
   if (p->stream) cudaStreamSynchronize(p->stream);
   if (p->d_res) cudaFree(p->d_res);
+  if (p->scrub) cudaFree(p->scrub);
   if (p->h_res) cudaFreeHost(p->h_res);
   for (auto &e : p->ev)
     if (e) cudaEventDestroy(e);
@@ -605,7 +627,8 @@ static int grid_for(const gs_probe *p, const void *fn, uint64_t total_tiles, int
 }
 
 int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t passes) {
-  if (!p || !slices || n == 0 || (passes & ~(GS_PROBE_WRITE | GS_PROBE_VERIFY)) || passes == 0)
+  if (!p || !slices || n == 0 || (passes & ~(GS_PROBE_WRITE | GS_PROBE_VERIFY | GS_PROBE_SCRUB)) ||
+      (passes & (GS_PROBE_WRITE | GS_PROBE_VERIFY)) == 0)
     return GS_E_INVAL;
   if (n > GS_PROBE_MAX_SLICES) return GS_E_LIMIT;
   if (p->pending) return GS_E_STATE;
@@ -681,6 +704,17 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
     ++launches;
   }
   GS_CUDA(cudaEventRecord(p->ev[1], p->stream));
+  if (passes & GS_PROBE_SCRUB) {
+    if (!p->scrub) {
+      GS_CUDA(cudaMalloc(&p->scrub, kScrubBytes + 256));
+      GS_CUDA(cudaMemsetAsync(p->scrub, 0, kScrubBytes + 256, p->stream));
+    }
+    probe_scrub_kernel<<<p->sms * 8, kThreads, 0, p->stream>>>(
+        (const uint4 *)p->scrub, kScrubBytes / 16, (uint32_t *)((char *)p->scrub + kScrubBytes));
+    GS_CUDA(cudaGetLastError());
+    ++launches;
+  }
+  GS_CUDA(cudaEventRecord(p->ev[4], p->stream));
   if (passes & GS_PROBE_VERIFY) {
     VerifyFn fn = verify_fn(p->verify_variant);
     int grid = 0;
@@ -734,7 +768,9 @@ int gs_probe_wait(gs_probe *p, gs_slice_result *results, uint32_t n, gs_probe_ti
     if (p->pending_passes & GS_PROBE_WRITE)
       GS_CUDA(cudaEventElapsedTime(&timing->write_ms, p->ev[0], p->ev[1]));
     if (p->pending_passes & GS_PROBE_VERIFY)
-      GS_CUDA(cudaEventElapsedTime(&timing->verify_ms, p->ev[1], p->ev[2]));
+      GS_CUDA(cudaEventElapsedTime(&timing->verify_ms, p->ev[4], p->ev[2]));
+    if (p->pending_passes & GS_PROBE_SCRUB)
+      GS_CUDA(cudaEventElapsedTime(&timing->scrub_ms, p->ev[1], p->ev[4]));
     timing->bytes = p->pending_bytes;
     timing->launches = p->pending_launches;
   }

@@ -25,10 +25,12 @@ class Timing:
     verify_ms: float
     bytes: int
     launches: int
+    scrub_ms: float = 0.0
 
     def gbps(self):
-        """2 algorithmic bytes per slice byte over both passes (SURVEY 8(d) metric 3)."""
-        t = self.write_ms + self.verify_ms
+        """2 algorithmic bytes per slice byte over both passes (SURVEY 8(d) metric 3); an L2
+        scrub between them counts as time, not as bytes."""
+        t = self.write_ms + self.verify_ms + self.scrub_ms
         n = (self.write_ms > 0) + (self.verify_ms > 0)
         return n * self.bytes / (t * 1e-3) / 1e9 if t > 0 else 0.0
 
@@ -99,7 +101,7 @@ class Probe:
         tm = L.ProbeTiming()
         L.check(self.lib.gs_probe_wait(self.h, res, self._n, C.byref(tm)), "gs_probe_wait")
         return ([SliceVerdict(r.mismatches, r.first_bad_byte, r.bit_flips) for r in res],
-                Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches))
+                Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches, tm.scrub_ms))
 
     def idle(self):
         return self.lib.gs_probe_poll(self.h) == L.GS_OK
@@ -139,7 +141,7 @@ def run_granted(cuda_ordinal, nbytes, seed):
     L.check(lib.gs_probe_run_granted(cuda_ordinal, nbytes, seed, C.byref(res), C.byref(tm)),
             "gs_probe_run_granted")
     return (SliceVerdict(res.mismatches, res.first_bad_byte, res.bit_flips),
-            Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches))
+            Timing(tm.write_ms, tm.verify_ms, tm.bytes, tm.launches, tm.scrub_ms))
 
 
 class ProbeScheduler:
@@ -156,8 +158,12 @@ class ProbeScheduler:
     thread (the daemon's probe thread does; Allocate only enqueues work for that thread).
     """
 
-    def __init__(self, probe: Probe, on_bad=None, max_pending=L.GS_PROBE_MAX_SLICES):
+    def __init__(self, probe: Probe, on_bad=None, max_pending=L.GS_PROBE_MAX_SLICES,
+                 scrub_below=512 << 20):
         self.probe = probe
+        # batches containing a slice this small get an L2 scrub between the passes: without it
+        # the 126 MB L2 would serve (part of) the read-back instead of HBM
+        self.scrub_below = scrub_below
         self.on_bad = on_bad
         self.max_pending = max_pending
         self.pending = []
@@ -204,7 +210,10 @@ class ProbeScheduler:
             self._collect()
         if self.inflight is None and self.pending:
             batch, self.pending = self.pending, []
-            self.probe.submit(batch)
+            passes = L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY
+            if min(s[1] for s in batch) < self.scrub_below:
+                passes |= L.GS_PROBE_SCRUB
+            self.probe.submit(batch, passes)
             self.inflight = batch
 
     def drain(self):

@@ -320,7 +320,7 @@ typedef struct gs_probe_timing {
   float verify_ms;   /* CUDA-event time of the load+compare pass               */
   uint64_t bytes;    /* sum of slice bytes in the batch                        */
   uint32_t launches; /* kernels launched for the batch                         */
-  uint32_t reserved;
+  float scrub_ms;    /* CUDA-event time of the L2 scrub between the passes     */
 } gs_probe_timing;
 
 #define GS_PROBE_MAX_SLICES 64 /* per batch (descriptors travel as kernel params) */
@@ -332,9 +332,13 @@ GS_API int gs_probe_sm_count(const gs_probe *p, int *sms);
 GS_API int gs_probe_mem_alloc(gs_probe *p, uint64_t bytes, void **dptr);
 GS_API int gs_probe_mem_free(gs_probe *p, void *dptr);
 GS_API int gs_probe_mem_info(gs_probe *p, uint64_t *free_bytes, uint64_t *total_bytes);
-/* Asynchronous on the probe's stream. passes: bit0 = write, bit1 = verify. */
+/* Asynchronous on the probe's stream. passes: bit0 = write, bit1 = verify, bit2 = scrub. */
 #define GS_PROBE_WRITE 1u
 #define GS_PROBE_VERIFY 2u
+/* Between the passes, stream 192 MiB through the 126 MB L2 so the read-back comes from
+ * DRAM even for slices smaller than the L2 (costs ~30 us and 192 MiB of HBM, allocated on
+ * first use). Meaningful together with at least one of the two passes.               */
+#define GS_PROBE_SCRUB 4u
 GS_API int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n,
                            uint32_t passes);
 /* Waits for the last submit; copies the per-slice results (n as submitted). */

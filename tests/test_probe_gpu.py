@@ -229,3 +229,21 @@ def test_store_pass_stays_inside_the_granted_range(probe, wvariant, nbytes):
     finally:
         probe.set_variant(write=102)
         probe.free(d)
+
+
+def test_l2_scrub_between_the_passes(probe, oracle_lib):
+    """GS_PROBE_SCRUB: same verdicts, a timed scrub kernel, and faults are still found."""
+    nbytes = 48 * MiB                        # smaller than the L2: the case the scrub exists for
+    d = probe.alloc(nbytes)
+    try:
+        both = L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY
+        v, tm = probe.run([(d, nbytes, 3)], both | L.GS_PROBE_SCRUB)
+        assert v[0].clean and tm.launches == 3 and tm.scrub_ms > 0 and tm.write_ms > 0 and tm.verify_ms > 0
+        assert probe.read(d, MiB) == oracle_bytes(oracle_lib, MiB, 3)
+        probe.inject(d, 40 * MiB + 8, 0x4)
+        v, tm = probe.run([(d, nbytes, 3)], L.GS_PROBE_VERIFY | L.GS_PROBE_SCRUB)
+        assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == (1, 40 * MiB + 8, 1)
+        with pytest.raises(L.GpushareError):
+            probe.run([(d, nbytes, 3)], L.GS_PROBE_SCRUB)          # a scrub alone is not a probe
+    finally:
+        probe.free(d)

@@ -13,6 +13,7 @@ class FakeEngine:
         assert not self.busy
         self.busy = True
         self.submitted.append(list(slices))
+        self.passes = getattr(self, "passes", []) + [passes]
 
     def idle(self):
         return not self.busy or self.finish_now
@@ -71,3 +72,15 @@ def test_bad_verdicts_reach_the_callback():
     s.grant(0x100, 16, 0, 7)
     s.drain()
     assert seen == [(7, 1)] and s.bad == 1
+
+
+def test_small_slices_get_an_l2_scrub():
+    e = FakeEngine()
+    e.finish_now = True
+    s = ProbeScheduler(e, scrub_below=1 << 20)
+    s.grant(0, 4 << 20, 0, 0)
+    s.drain()
+    s.grant(0, 4 << 20, 0, 0)
+    s.grant(0x1000000, 64 << 10, 0, 1)
+    s.drain()
+    assert e.passes == [3, 7]            # write+verify; write+scrub+verify once a slice is below the bar
