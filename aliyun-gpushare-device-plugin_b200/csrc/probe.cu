@@ -19,6 +19,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -392,17 +393,18 @@ __global__ void probe_inject_kernel(uint32_t *word, uint32_t mask) { *word ^= ma
 // the write-back running underneath it.
 constexpr uint64_t kScrubBytes = 192ull << 20;  // L2 is 126 MB
 __global__ void __launch_bounds__(kThreads)
-    probe_scrub_kernel(const uint4 *__restrict__ buf, uint64_t n_vec, uint32_t *sink) {
+    probe_scrub_kernel(uint4 *__restrict__ buf, uint64_t n_vec, uint32_t mode) {
   const uint64_t stride = (uint64_t)gridDim.x * kThreads;
-  uint32_t acc = 0;
   uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
-  for (; i + 3 * stride < n_vec; i += 4 * stride) {
-    const uint4 a = ld128<0>(buf + i, 0), b = ld128<0>(buf + i + stride, 0);
-    const uint4 c = ld128<0>(buf + i + 2 * stride, 0), d = ld128<0>(buf + i + 3 * stride, 0);
-    acc ^= a.x ^ a.w ^ b.x ^ b.w ^ c.x ^ c.w ^ d.x ^ d.w;
+  if (mode == 0) {
+    // stores also displace the slice, but leave 192 MiB of dirty lines behind for the load pass
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (; i < n_vec; i += stride) st128<0>(buf + i, z, 0);
+  } else {
+    uint32_t acc = 0;
+    for (; i < n_vec; i += stride) acc ^= ld128<0>(buf + i, 0).x;
+    if (acc == 0x9E3779B9u) buf[0].x = acc;  // zero-filled buffer: never taken, keeps the loads
   }
-  for (; i < n_vec; i += stride) acc ^= ld128<0>(buf + i, 0).x;
-  if (acc == 0x9E3779B9u) *sink = acc;  // the buffer is zero-filled: never taken, keeps the loads
 }
 
 // ---- variant dispatch ----------------------------------------------------------
@@ -489,6 +491,7 @@ struct gs_probe {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   void *scrub = nullptr;  // kScrubBytes, allocated on the first GS_PROBE_SCRUB
+  uint32_t scrub_mode = 1;  // 1 = stream loads (default), 0 = store zeros (GS_PROBE_SCRUB_MODE)
   DevResult *d_res = nullptr;
   DevResult *h_res = nullptr;  // pinned
   uint32_t pending_n = 0;
@@ -529,6 +532,7 @@ int gs_probe_open(int cuda_ordinal, gs_probe **out) {
   gs_probe *p = new (std::nothrow) gs_probe();
   if (!p) return GS_E_INVAL;
   p->dev = cuda_ordinal;
+  if (const char *m = getenv("GS_PROBE_SCRUB_MODE")) p->scrub_mode = (uint32_t)atoi(m);
   cudaError_t e = cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, cuda_ordinal);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking);
   for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
@@ -709,8 +713,8 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
       GS_CUDA(cudaMalloc(&p->scrub, kScrubBytes + 256));
       GS_CUDA(cudaMemsetAsync(p->scrub, 0, kScrubBytes + 256, p->stream));
     }
-    probe_scrub_kernel<<<p->sms * 8, kThreads, 0, p->stream>>>(
-        (const uint4 *)p->scrub, kScrubBytes / 16, (uint32_t *)((char *)p->scrub + kScrubBytes));
+    probe_scrub_kernel<<<p->sms * 8, kThreads, 0, p->stream>>>((uint4 *)p->scrub, kScrubBytes / 16,
+                                                               p->scrub_mode);
     GS_CUDA(cudaGetLastError());
     ++launches;
   }
