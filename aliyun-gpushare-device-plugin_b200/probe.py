@@ -176,6 +176,7 @@ class ProbeScheduler:
         self.coalesced = 0
         self.write_ms = 0.0
         self.verify_ms = 0.0
+        self.scrub_ms = 0.0
         self.bad = 0
 
     def grant(self, base, nbytes, seed, tag=0):
@@ -197,6 +198,7 @@ class ProbeScheduler:
         self.bytes_probed += tm.bytes
         self.write_ms += tm.write_ms
         self.verify_ms += tm.verify_ms
+        self.scrub_ms += tm.scrub_ms
         for s, v in zip(self.inflight, verdicts):
             if not v.clean:
                 self.bad += 1
@@ -224,5 +226,5 @@ class ProbeScheduler:
             self.pump()
 
     def gbps(self):
-        t = self.write_ms + self.verify_ms
+        t = self.write_ms + self.verify_ms + self.scrub_ms
         return 2 * self.bytes_probed / (t * 1e-3) / 1e9 if t > 0 else 0.0
