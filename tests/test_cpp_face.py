@@ -12,3 +12,17 @@ def test_cpp_consumer(tmp_path):
                     "-Wl,-rpath," + os.path.dirname(CORE_SO)], check=True)
     out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0 and "CPP FACE OK" in out.stdout, out.stdout + out.stderr
+
+
+def test_host_core_under_address_and_ub_sanitizers(tmp_path):
+    """allocate/table/gosem/plugin/errors rebuilt with ASan + UBSan and driven with random
+    tables, health marks, pods and (often malformed) requests: no out-of-bounds, overflow or leak."""
+    csrc = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc")
+    exe = tmp_path / "fuzz_core"
+    srcs = [os.path.join(csrc, f) for f in ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp")]
+    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
+                    "-I" + os.path.join(ROOT, "include"), "-I" + csrc,
+                    os.path.join(ROOT, "tests", "cpp", "fuzz_core.cpp")] + srcs + ["-o", str(exe), "-lpthread"],
+                   check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "FUZZ CORE OK" in out.stdout, (out.stdout + out.stderr)[-3000:]
