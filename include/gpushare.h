@@ -177,9 +177,11 @@ GS_API uint64_t gs_law_generation(const gs_table *t); /* bumps on every change *
 GS_API size_t gs_law_payload_size(const gs_table *t);
 /* Encodes the whole ListAndWatchResponse{devices=1} into buf.                */
 GS_API int gs_law_encode(const gs_table *t, uint8_t *buf, size_t cap, size_t *len);
-/* Zero-copy form: borrowed pre-encoded segments (one per GPU) whose
- * concatenation is the response; valid until the next health change on that
- * GPU or gs_table_free.                                                        */
+/* Zero-copy form: borrowed pre-encoded segments (one per GPU) whose concatenation is the
+ * response. A segment of a GPU with unhealthy devices is rebuilt by the next gs_law_payload
+ * call after a health change, so this form is for ONE sender (kubelet opens one stream);
+ * several concurrent senders use gs_law_encode, which copies under the table's lock.
+ * Segments of all-healthy GPUs never move until gs_table_free.                           */
 typedef struct gs_iovec {
   const uint8_t *base;
   size_t len;

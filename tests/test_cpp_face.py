@@ -26,3 +26,17 @@ def test_host_core_under_address_and_ub_sanitizers(tmp_path):
                    check=True)
     out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "FUZZ CORE OK" in out.stdout, (out.stdout + out.stderr)[-3000:]
+
+
+def test_host_core_under_thread_sanitizer(tmp_path):
+    """Allocate from four threads, health marks, two ListAndWatch senders and the health wait, all
+    on one table/plugin, under TSan: no data race."""
+    csrc = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc")
+    exe = tmp_path / "race_core"
+    srcs = [os.path.join(csrc, f) for f in ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp")]
+    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-I" + os.path.join(ROOT, "include"),
+                    "-I" + csrc, os.path.join(ROOT, "tests", "cpp", "race_core.cpp")] + srcs +
+                   ["-o", str(exe), "-lpthread"], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "RACE CORE OK" in out.stdout and "WARNING: ThreadSanitizer" not in out.stderr, \
+        (out.stdout + out.stderr)[-4000:]
