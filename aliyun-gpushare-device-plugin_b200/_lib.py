@@ -71,6 +71,24 @@ class ProbeTiming(C.Structure):
                 ("launches", C.c_uint32), ("scrub_ms", C.c_float)]
 
 
+ServerAllocateFn = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint8), C.c_size_t,
+                               C.POINTER(C.c_uint8), C.c_size_t, C.POINTER(C.c_size_t))
+ServerDecisionFn = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(AllocResult))
+
+
+class ServerConfig(C.Structure):
+    _fields_ = [("socket_path", C.c_char_p), ("allocate", ServerAllocateFn),
+                ("on_decision", ServerDecisionFn), ("user", C.c_void_p),
+                ("max_request_bytes", C.c_size_t)]
+
+
+class ServerStats(C.Structure):
+    _fields_ = [("connections", C.c_uint64), ("requests", C.c_uint64),
+                ("allocate_calls", C.c_uint64), ("law_messages", C.c_uint64),
+                ("protocol_errors", C.c_uint64), ("bytes_in", C.c_uint64),
+                ("bytes_out", C.c_uint64)]
+
+
 _P = C.POINTER
 _vp, _sz, _u32, _u64, _i32, _i64, _int = (C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint64,
                                           C.c_int32, C.c_int64, C.c_int)
@@ -135,6 +153,18 @@ SIGNATURES = {
     "gs_plugin_notify_health": (_int, [_vp]),
     "gs_plugin_stop": (_int, [_vp]),
     "gs_plugin_stopped": (_int, [_vp]),
+    "gs_server_start": (_int, [_vp, _P(ServerConfig), _P(_vp)]),
+    "gs_server_stop": (_int, [_vp]),
+    "gs_server_get_stats": (_int, [_vp, _P(ServerStats)]),
+    "gs_register": (_int, [C.c_char_p, C.c_char_p, C.c_char_p, _u32]),
+    "gs_grpc_client_connect": (_int, [C.c_char_p, _u32, _P(_vp)]),
+    "gs_grpc_client_close": (None, [_vp]),
+    "gs_grpc_client_unary": (_int, [_vp, C.c_char_p, C.c_char_p, _sz, _vp, _sz, _P(_sz), _P(_i32),
+                                    C.c_char_p, _sz]),
+    "gs_grpc_client_stream_open": (_int, [_vp, C.c_char_p, C.c_char_p, _sz, _P(_u32)]),
+    "gs_grpc_client_stream_next": (_int, [_vp, _u32, _vp, _sz, _P(_sz), _P(_i32), _u32]),
+    "gs_grpc_client_stream_cancel": (_int, [_vp, _u32]),
+    "gs_grpc_last_error": (C.c_char_p, []),
     "gs_probe_open": (_int, [_int, _P(_vp)]),
     "gs_probe_close": (_int, [_vp]),
     "gs_probe_sm_count": (_int, [_vp, _P(_int)]),

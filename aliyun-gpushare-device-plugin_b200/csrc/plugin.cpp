@@ -14,6 +14,7 @@
 // reserved capacity: applying the "assigned" patch never allocates.
 #include <string.h>
 #include <time.h>
+#include <unistd.h>
 
 #include <atomic>
 #include <chrono>
@@ -60,6 +61,14 @@ struct gs_plugin {
   std::mutex health_mu;
   std::condition_variable health_cv;         // m.health channel
   std::atomic<bool> stopped{false};          // m.stop channel
+  std::vector<int> wake_fds;                 // eventfds of transports serving this plugin
+
+  void wake() {  // health_mu held
+    const uint64_t one = 1;
+    for (int fd : wake_fds)
+      if (write(fd, &one, sizeof(one)) < 0) {
+      }
+  }
 
   void refresh_view(size_t i) {
     const StoredPod &p = pods[i];
@@ -74,6 +83,22 @@ struct gs_plugin {
     v.ann_assigned = p.has_assigned ? view(p.assigned) : gs_str{nullptr, 0};
   }
 };
+
+namespace gs_internal {
+void plugin_add_wake_fd(gs_plugin *p, int fd) {
+  std::lock_guard<std::mutex> lk(p->health_mu);
+  p->wake_fds.push_back(fd);
+}
+void plugin_remove_wake_fd(gs_plugin *p, int fd) {
+  std::lock_guard<std::mutex> lk(p->health_mu);
+  for (size_t i = 0; i < p->wake_fds.size(); ++i)
+    if (p->wake_fds[i] == fd) {
+      p->wake_fds.erase(p->wake_fds.begin() + (long)i);
+      break;
+    }
+}
+gs_table *plugin_table(gs_plugin *p) { return p->table; }
+}  // namespace gs_internal
 
 extern "C" {
 
@@ -219,6 +244,7 @@ int gs_plugin_notify_health(gs_plugin *p) {
   if (!p) return GS_E_INVAL;
   {
     std::lock_guard<std::mutex> lk(p->health_mu);
+    p->wake();
   }
   p->health_cv.notify_all();
   return GS_OK;
@@ -229,6 +255,7 @@ int gs_plugin_stop(gs_plugin *p) {
   {
     std::lock_guard<std::mutex> lk(p->health_mu);
     p->stopped.store(true);
+    p->wake();
   }
   p->health_cv.notify_all();
   return GS_OK;

@@ -297,6 +297,78 @@ GS_API int gs_plugin_notify_health(gs_plugin *p); /* wake waiters after gs_law_m
 GS_API int gs_plugin_stop(gs_plugin *p);          /* close(m.stop), server.go:152 */
 GS_API int gs_plugin_stopped(const gs_plugin *p);
 
+/* ---- kubelet-facing transport (server.go:114-177,232-265) ------------------ *
+ * gRPC over HTTP/2 on a unix socket, native: the reference gets it from
+ * google.golang.org/grpc (go.mod:48). The server routes v1beta1.DevicePlugin
+ * to the gs_plugin_* entry points above on one serving thread; ListAndWatch
+ * sends borrow gs_law_payload's segments, so while a server runs on a table it
+ * is that table's one gs_law_payload caller (others use gs_law_encode).
+ * Limits: request messages up to max_request_bytes (default 64 MiB; grpc-go's
+ * default of 4 MiB would refuse a whole B200 at MiB granularity, H12), header
+ * blocks up to 256 KiB, Huffman-coded header strings restricted to printable
+ * ASCII (see csrc/hpack.h), no message compression (UNIMPLEMENTED, as grpc-go
+ * answers without a registered decompressor).                                  */
+typedef struct gs_server gs_server;
+/* Optional replacement for the Allocate body, for callers whose pod source is
+ * the network (podmanager.go:187-245, allocate.go:136): called on the serving
+ * thread with the AllocateRequest bytes; writes the AllocateResponse bytes.
+ * GS_E_NOSPACE with *resp_len = required size asks for a larger buffer.        */
+typedef int (*gs_server_allocate_fn)(void *user, const uint8_t *req, size_t req_len,
+                                     uint8_t *resp, size_t resp_cap, size_t *resp_len);
+/* Optional hook after each decision of the built-in Allocate (e.g. queue a
+ * slice probe for the granted range). Runs on the serving thread.              */
+typedef void (*gs_server_decision_fn)(void *user, const gs_alloc_result *decision);
+typedef struct gs_server_config {
+  const char *socket_path;        /* e.g. GS_DEVICE_PLUGIN_PATH GS_SERVER_SOCK_NAME */
+  gs_server_allocate_fn allocate; /* NULL: gs_plugin_allocate on the in-memory pod store */
+  gs_server_decision_fn on_decision;
+  void *user;
+  size_t max_request_bytes;       /* 0 = 64 MiB */
+} gs_server_config;
+typedef struct gs_server_stats {
+  uint64_t connections, requests, allocate_calls, law_messages, protocol_errors;
+  uint64_t bytes_in, bytes_out;   /* of connections already closed */
+} gs_server_stats;
+/* Start (server.go:114-142): removes a stale socket, listens, serves, and dials
+ * itself (5 s) before returning. GS_E_STATE: cannot bind; GS_E_TIMEOUT: the
+ * self-dial failed.                                                            */
+GS_API int gs_server_start(gs_plugin *p, const gs_server_config *cfg, gs_server **out);
+/* Stop (server.go:145-155): gs_plugin_stop (open ListAndWatch streams end with
+ * status OK), GOAWAY, close, remove the socket, free the server.               */
+GS_API int gs_server_stop(gs_server *s);
+GS_API int gs_server_get_stats(const gs_server *s, gs_server_stats *out);
+
+/* Register (server.go:158-177): dial kubelet's socket (blocking, timeout), send
+ * RegisterRequest{version "v1beta1", endpoint, resource_name}, options unset.
+ * GS_E_TIMEOUT: no kubelet; GS_E_STATE: non-OK status (gs_grpc_last_error).    */
+GS_API int gs_register(const char *kubelet_socket, const char *endpoint,
+                       const char *resource_name, uint32_t timeout_ms);
+
+/* The kubelet side of the same transport, for Register above, tests and
+ * benchmarks: unary calls and server streams over one connection. One caller at
+ * a time per client. No counterpart in the reference beyond dial()
+ * (server.go:252-265).                                                         */
+typedef struct gs_grpc_client gs_grpc_client;
+GS_API int gs_grpc_client_connect(const char *unix_path, uint32_t timeout_ms,
+                                  gs_grpc_client **out);
+GS_API void gs_grpc_client_close(gs_grpc_client *c);
+/* GS_OK when the call completed; *grpc_status then carries the gRPC code (0 =
+ * OK, response in resp) and `message` the grpc-message, NUL-terminated.        */
+GS_API int gs_grpc_client_unary(gs_grpc_client *c, const char *method_path,
+                                const uint8_t *req, size_t req_len, uint8_t *resp,
+                                size_t resp_cap, size_t *resp_len, int32_t *grpc_status,
+                                char *message, size_t message_cap);
+GS_API int gs_grpc_client_stream_open(gs_grpc_client *c, const char *method_path,
+                                      const uint8_t *req, size_t req_len, uint32_t *stream);
+/* Next message of a server stream. GS_OK: a message; GS_E_NOSPACE: it needs
+ * *resp_len bytes (still queued); GS_E_TIMEOUT; GS_E_STATE: the stream ended,
+ * *grpc_status holds its status (or -1 when the connection broke).             */
+GS_API int gs_grpc_client_stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp,
+                                      size_t resp_cap, size_t *resp_len,
+                                      int32_t *grpc_status, uint32_t timeout_ms);
+GS_API int gs_grpc_client_stream_cancel(gs_grpc_client *c, uint32_t stream);
+GS_API const char *gs_grpc_last_error(void); /* thread-local, valid until the next call */
+
 /* ---- slice probe (K1; no counterpart in the reference) -------------------- *
  * Writes pattern(i, seed) over exactly the granted HBM range as 128-bit
  * coalesced stores, reads it back with 128-bit loads, compares, and reduces

@@ -1,0 +1,337 @@
+"""The native gRPC transport (csrc/hpack.h, h2conn.h, grpc_server.cpp, grpc_client.cpp):
+RFC 7541 known answers for the header codec, then interoperability in all four pairings of
+{grpcio, native} x {client, server} over real unix sockets, on the reference's own surface
+(Register, the five RPCs, a streamed ListAndWatch with a health event)."""
+import os
+import subprocess
+import tempfile
+import threading
+import time
+
+import grpc
+import pytest
+
+from gpushare_b200 import _lib as L
+from gpushare_b200 import api
+from gpushare_b200.grpc_harness import DevicePluginServer, KubeletStub, encode_register_request
+from gpushare_b200.native_transport import NativeClient, NativeDevicePluginServer, RpcError
+from oracle import ref_model as R
+from tests.helpers import product_for_case
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc")
+
+
+@pytest.fixture
+def sockdir():
+    with tempfile.TemporaryDirectory(prefix="gs") as d:
+        yield d
+
+
+def test_hpack_rfc7541_known_answers(tmp_path):
+    """Appendix C examples (integers, literals, the request series with and without Huffman,
+    the response series with evictions) plus malformed blocks, under ASan/UBSan."""
+    exe = str(tmp_path / "hpack_kat")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined",
+                    "-fno-sanitize-recover=undefined", "-I" + CSRC,
+                    os.path.join(ROOT, "tests", "cpp", "hpack_kat.cpp"), "-o", exe], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.count("ok  ") == 15 and "FAIL" not in r.stdout
+
+
+def _golden(golden_cases, name="G1-binpack-1"):
+    return next(x for x in golden_cases if x["name"] == name)
+
+
+def test_grpcio_client_against_native_server(golden_cases, sockdir):
+    """What kubelet does, with grpc-core as the client (Huffman strings, a dynamic table,
+    BDP pings): registration, every RPC, the watch stream, stop."""
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    kubelet = KubeletStub(os.path.join(sockdir, "kubelet.sock"))
+    kubelet.start()
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "aliyungpushare.sock"))
+    assert not srv.python_allocate
+    try:
+        srv.Serve(kubelet.socket)
+        assert kubelet.wait_registered(5)
+        assert kubelet.registered[0] == encode_register_request("v1beta1", "aliyungpushare.sock",
+                                                                "aliyun.com/gpu-mem")
+        ch = KubeletStub.connect(srv.socket)
+        assert KubeletStub.method(ch, "GetDevicePluginOptions")(b"") == b""
+        assert KubeletStub.method(ch, "PreStartContainer")(b"\x0a\x03abc") == b""
+        with pytest.raises(grpc.RpcError) as e:
+            KubeletStub.method(ch, "GetPreferredAllocation")(b"")
+        assert e.value.code() == grpc.StatusCode.UNIMPLEMENTED and e.value.details() == "implement me"
+        with pytest.raises(grpc.RpcError) as e:
+            KubeletStub.method(ch, "NoSuchMethod")(b"")
+        assert e.value.code() == grpc.StatusCode.UNIMPLEMENTED
+        assert e.value.details() == "unknown method NoSuchMethod for service v1beta1.DevicePlugin"
+        with pytest.raises(grpc.RpcError) as e:
+            ch.unary_unary("/v1beta1.Registration/Register")(b"")
+        assert e.value.details() == "unknown service v1beta1.Registration"
+        alloc = KubeletStub.method(ch, "Allocate")
+        for st in c["steps"]:                        # same socket, same answers as the fixture
+            resp = alloc(R.encode_allocate_request(st["request"]))
+            assert R.decode_allocate_response(resp) == st["expect_envs"]
+        with pytest.raises(grpc.RpcError) as e:      # bytes that are not an AllocateRequest
+            alloc(b"\x0a\xff\xff\xff\xff\x0f")
+        assert e.value.code() == grpc.StatusCode.INTERNAL
+        stream = KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")
+        first = R.decode_list_and_watch(next(stream))
+        assert len(first) == 128 and all(h == "Healthy" for _, h in first)
+        # Allocate keeps working on the same connection while the stream is open
+        assert R.decode_allocate_response(alloc(R.encode_allocate_request(c["steps"][-1]["request"]))) \
+            == c["steps"][-1]["expect_envs"]
+        plug.unhealthy(3)
+        second = R.decode_list_and_watch(next(stream))
+        assert [h for i, h in second if i.startswith("GPU-00000003")] == ["Unhealthy"] * 16
+        assert sum(h == "Unhealthy" for _, h in second) == 16
+        st = srv.stats()
+        assert st["law_messages"] == 2 and st["allocate_calls"] == len(c["steps"]) + 2
+        assert st["protocol_errors"] == 0
+        # Stop: the stream ends with status OK (ListAndWatch returns nil on m.stop)
+        srv.Stop()
+        assert list(stream) == []
+        assert stream.code() == grpc.StatusCode.OK
+        ch.close()
+    finally:
+        srv.Stop()
+        kubelet.stop()
+    assert not os.path.exists(srv.socket)
+
+
+def test_native_client_against_grpcio_server(golden_cases, sockdir):
+    """The native client against grpc-core as the server: our Register against the kubelet
+    stub, and the plugin surface served by the grpcio harness."""
+    lib = L.load()
+    kubelet = KubeletStub(os.path.join(sockdir, "kubelet.sock"))
+    kubelet.start()
+    try:
+        assert lib.gs_register(kubelet.socket.encode(), b"aliyungpushare.sock", b"aliyun.com/gpu-mem", 5000) == 0
+        assert kubelet.registered == [encode_register_request("v1beta1", "aliyungpushare.sock",
+                                                              "aliyun.com/gpu-mem")]
+        # a method the kubelet stub does not serve: the status comes back, not a hang
+        with NativeClient(kubelet.socket) as cl:
+            with pytest.raises(RpcError) as e:
+                cl.call("Nope", b"", service="v1beta1.Registration")
+            assert e.value.code == 12
+    finally:
+        kubelet.stop()
+    t0 = time.time()
+    assert lib.gs_register(os.path.join(sockdir, "absent.sock").encode(), b"e", b"r", 300) == L.GS_E_TIMEOUT
+    assert 0.25 < time.time() - t0 < 3
+
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = DevicePluginServer(plug, os.path.join(sockdir, "aliyungpushare.sock"))
+    srv.Start()
+    try:
+        with NativeClient(srv.socket) as cl:
+            assert cl.call("GetDevicePluginOptions") == b""
+            for st in c["steps"]:
+                assert R.decode_allocate_response(cl.call("Allocate", R.encode_allocate_request(st["request"]))) \
+                    == st["expect_envs"]
+            with pytest.raises(RpcError) as e:
+                cl.call("GetPreferredAllocation")
+            assert (e.value.code, e.value.message) == (12, "implement me")
+            sid = cl.open_stream("ListAndWatch")
+            assert len(R.decode_list_and_watch(cl.next_message(sid))) == 128
+            assert cl.call("PreStartContainer", b"\x0a\x01x") == b""      # unary beside the stream
+            plug.unhealthy(1)
+            second = R.decode_list_and_watch(cl.next_message(sid))
+            assert sum(h == "Unhealthy" for _, h in second) == 16
+            with pytest.raises(TimeoutError):
+                cl.next_message(sid, timeout_ms=100)
+            cl.cancel(sid)
+    finally:
+        srv.Stop()
+
+
+def test_native_both_sides_large_messages(sockdir):
+    """One B200 at MiB granularity: an 11.3 MB ListAndWatchResponse out (flow control, frame
+    splitting, borrowed segments) and a 2 MB AllocateRequest in, byte-exact."""
+    uuid = "GPU-0f9b9cf4-2b1c-4a3e-9c1d-5e2f6a7b8c9d"
+    units = 183359
+    table = api.DeviceTable([uuid], units, api.MiB)
+    plug = api.NvidiaDevicePlugin(table, "node-a")
+    pods = []
+    for k, gib in enumerate((40, 1)):
+        pods.append({"metadata": {"uid": "u%d" % k, "namespace": "default", "name": "t%d" % k, "annotations": {
+            "ALIYUN_COM_GPU_MEM_IDX": "0", "ALIYUN_COM_GPU_MEM_ASSUME_TIME": str(1000 + k),
+            "ALIYUN_COM_GPU_MEM_ASSIGNED": "false"}},
+            "spec": {"nodeName": "node-a", "containers": [{"name": "c", "resources": {"limits": {
+                "aliyun.com/gpu-mem": str(gib * 1024)}}}]}, "status": {"phase": "Pending"}})
+    plug.set_pods([api.Pod.from_k8s(p) for p in pods])
+    seen = []
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"),
+                                   on_decision=lambda *a: seen.append(a))
+    srv.Start()
+    try:
+        with NativeClient(srv.socket) as cl:
+            sid = cl.open_stream("ListAndWatch")
+            want = table.list_and_watch_bytes()
+            assert len(want) == 11257148
+            got = cl.next_message(sid, timeout_ms=20000)
+            assert got == want
+            ids = ["%s-_-%d" % (uuid, j) for j in range(40 * 1024)]
+            req = R.encode_allocate_request([ids])
+            assert len(req) > 2_000_000
+            envs = R.decode_allocate_response(cl.call("Allocate", req))
+            assert envs == [{"NVIDIA_VISIBLE_DEVICES": "0", "ALIYUN_COM_GPU_MEM_IDX": "0",
+                             "ALIYUN_COM_GPU_MEM_POD": "40960", "ALIYUN_COM_GPU_MEM_CONTAINER": "40960",
+                             "ALIYUN_COM_GPU_MEM_DEV": str(units)}]
+            assert seen == [("matched", 0, 0, 40960)]
+            assert plug.get_pod(0).ann_assigned == "true"
+            # a health change while nothing is in flight: exactly one fresh list
+            plug.unhealthy(0)
+            second = cl.next_message(sid, timeout_ms=20000)
+            assert second == table.list_and_watch_bytes() and len(second) == len(want) + 2 * units
+            with pytest.raises(TimeoutError):
+                cl.next_message(sid, timeout_ms=200)
+        # the same list through grpc-core's flow control (64 KiB windows growing by BDP)
+        ch = KubeletStub.connect(srv.socket)
+        stream = KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")
+        assert next(stream) == table.list_and_watch_bytes()
+        stream.cancel()
+        ch.close()
+    finally:
+        srv.Stop()
+    # a request beyond the limit is refused with a status, and the connection survives
+    plug2 = api.NvidiaDevicePlugin(table, "node-a")
+    small = NativeDevicePluginServer(plug2, os.path.join(sockdir, "q.sock"), max_request_bytes=4096)
+    small.Start()
+    try:
+        with NativeClient(small.socket) as cl:
+            with pytest.raises(RpcError) as e:
+                cl.call("Allocate", req)
+            assert e.value.code == 8 and "larger than max" in e.value.message
+            assert cl.call("GetDevicePluginOptions") == b""
+        ch = KubeletStub.connect(small.socket)
+        with pytest.raises(grpc.RpcError) as e:
+            KubeletStub.method(ch, "Allocate")(req)
+        assert e.value.code() == grpc.StatusCode.RESOURCE_EXHAUSTED
+        assert KubeletStub.method(ch, "GetDevicePluginOptions")(b"") == b""
+        ch.close()
+    finally:
+        small.Stop()
+
+
+def test_python_allocate_behind_native_server(golden_cases, sockdir):
+    """A plugin whose Allocate is Python (the cluster plugin, the daemon's probe hook) is
+    called back with the request bytes; its failures become statuses, not dead connections."""
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    decisions = []
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"), on_allocate=decisions.append)
+    assert srv.python_allocate
+    srv.Start()
+    try:
+        with NativeClient(srv.socket) as cl:
+            for st in c["steps"]:
+                assert R.decode_allocate_response(cl.call("Allocate", R.encode_allocate_request(st["request"]))) \
+                    == st["expect_envs"]
+            assert [d.kind for d in decisions][:3] == ["matched"] * 3
+            with pytest.raises(RpcError) as e:
+                cl.call("Allocate", b"\x0a\xff\xff\xff\xff\x0f")
+            assert e.value.code == 13
+            plug.Allocate = lambda request: 1 / 0
+            with pytest.raises(RpcError) as e:
+                cl.call("Allocate", b"")
+            assert e.value.code == 2
+            assert cl.call("GetDevicePluginOptions") == b""
+    finally:
+        srv.Stop()
+
+
+def test_many_calls_and_two_clients(golden_cases, sockdir):
+    """Several hundred calls on one connection (HPACK dynamic table churn on the grpc-core
+    side), two connections at once, and a client that vanishes mid-stream."""
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    try:
+        req = R.encode_allocate_request(c["steps"][0]["request"])
+        ch = KubeletStub.connect(srv.socket)
+        alloc = KubeletStub.method(ch, "Allocate")
+        first = alloc(req, metadata=(("x-trace", "0"),))
+        errors = []
+
+        def hammer():
+            try:
+                with NativeClient(srv.socket) as cl:
+                    for _ in range(300):
+                        R.decode_allocate_response(cl.call("Allocate", req))
+            except Exception as e:                      # noqa: BLE001
+                errors.append(e)
+        t = threading.Thread(target=hammer)
+        t.start()
+        for i in range(300):
+            r = alloc(req, metadata=(("x-trace", str(i)), ("x-long", "v" * (i % 200))))
+            assert len(R.decode_allocate_response(r)) == len(R.decode_allocate_response(first)) == 1
+        t.join(30)
+        assert not errors and not t.is_alive()
+        # a client that opens the watch stream and disappears
+        cl = NativeClient(srv.socket)
+        sid = cl.open_stream("ListAndWatch")
+        cl.next_message(sid)
+        cl.close()
+        assert KubeletStub.method(ch, "GetDevicePluginOptions")(b"") == b""
+        plug.unhealthy(0)                               # nobody is listening: must not wedge
+        assert KubeletStub.method(ch, "GetDevicePluginOptions")(b"") == b""
+        assert srv.stats()["protocol_errors"] == 0
+        ch.close()
+    finally:
+        srv.Stop()
+
+
+def test_server_rejects_garbage_and_survives(golden_cases, sockdir):
+    """Bytes that are not HTTP/2, a bad preface, an oversized header frame, a truncated
+    frame: the connection is dropped, the server keeps serving others."""
+    import socket as pysock
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    preface = b"PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n"
+    try:
+        for junk in (b"GET / HTTP/1.1\r\nHost: x\r\n\r\n",
+                     preface + b"\x00\x00\x00\x04\x00\x00\x00\x00\x00" + b"\x01\xff\xff\x01\x05\x00\x00\x00\x01" + b"x" * 16,
+                     preface + b"\x00\x00\x05\x01\x04\x00\x00\x00\x01\x80\x80\x80\x80\x80",   # HPACK: index 0
+                     preface + b"\x00\x00\x04\x08\x00\x00\x00\x00\x00\x00\x00\x00\x00",       # WINDOW_UPDATE 0
+                     preface + b"\x00\x00\x08\x06\x00\x00\x00\x00\x01" + b"12345678",          # PING on a stream
+                     preface + b"\x00\x00\x03\x00\x00\x00\x00\x00\x00abc",                    # DATA on stream 0
+                     preface + b"\x00\x00\x03\x00\x00\x00\x00\x00\x05abc",                    # DATA on an idle stream
+                     preface + b"\x00\x40\x00"):                                               # truncated header
+            s = pysock.socket(pysock.AF_UNIX, pysock.SOCK_STREAM)
+            s.settimeout(5)
+            s.connect(srv.socket)
+            s.sendall(junk)
+            s.shutdown(pysock.SHUT_WR)
+            while s.recv(65536):                        # server says what it has to say, then closes
+                pass
+            s.close()
+        with NativeClient(srv.socket) as cl:
+            assert cl.call("GetDevicePluginOptions") == b""
+        assert srv.stats()["connections"] >= 9
+    finally:
+        srv.Stop()
+
+
+def test_abi_argument_checks(sockdir):
+    lib = L.load()
+    import ctypes as C
+    h = C.c_void_p()
+    assert lib.gs_server_start(None, None, C.byref(h)) == L.GS_E_INVAL
+    assert lib.gs_server_stop(None) == L.GS_E_INVAL
+    assert lib.gs_grpc_client_connect(None, 10, C.byref(h)) == L.GS_E_INVAL
+    assert lib.gs_grpc_client_connect(("x" * 200).encode(), 10, C.byref(h)) == L.GS_E_INVAL
+    assert lib.gs_register(None, b"a", b"b", 10) == L.GS_E_INVAL
+    lib.gs_grpc_client_close(None)
+    table = api.DeviceTable(["GPU-a"], 4, api.GiB)
+    plug = api.NvidiaDevicePlugin(table, "n")
+    cfg = L.ServerConfig()
+    cfg.socket_path = os.path.join(sockdir, "no", "such", "dir", "s.sock").encode()
+    assert lib.gs_server_start(plug.h, C.byref(cfg), C.byref(h)) == L.GS_E_STATE
