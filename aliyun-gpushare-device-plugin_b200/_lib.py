@@ -163,6 +163,7 @@ SIGNATURES = {
                                     C.c_char_p, _sz]),
     "gs_grpc_client_stream_open": (_int, [_vp, C.c_char_p, C.c_char_p, _sz, _P(_u32)]),
     "gs_grpc_client_stream_next": (_int, [_vp, _u32, _vp, _sz, _P(_sz), _P(_i32), _u32]),
+    "gs_grpc_client_stream_next_borrow": (_int, [_vp, _u32, _P(_vp), _P(_sz), _P(_i32), _u32]),
     "gs_grpc_client_stream_cancel": (_int, [_vp, _u32]),
     "gs_grpc_last_error": (C.c_char_p, []),
     "gs_probe_open": (_int, [_int, _P(_vp)]),

@@ -485,6 +485,10 @@ class NvidiaDevicePlugin:
         self.table.mark_unhealthy_gpu(gpu)
         L.check(self.lib.gs_plugin_notify_health(self.h))
 
+    def notify_health(self):
+        """Wake ListAndWatch senders after a health change made on the table directly."""
+        L.check(self.lib.gs_plugin_notify_health(self.h))
+
     def unhealthy_device(self, fake_id):
         """m.unhealthy(dev) for one fake device, the reference's granularity
         (server.go:195-197)."""

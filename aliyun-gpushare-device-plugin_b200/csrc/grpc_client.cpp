@@ -372,13 +372,19 @@ thread_local std::string g_last_error;
 
 // Copies the next complete message of the stream to the caller. GS_OK, GS_E_NOSPACE (the
 // message stays queued, *len = its size), or 1 = no complete message buffered yet.
-int take_message(CStream &s, uint8_t *out, size_t cap, size_t *len) {
+int take_message(CStream &s, uint8_t *out, size_t cap, size_t *len, const uint8_t **borrow = nullptr) {
   RBuf &d = s.data;
+  d.compact();
   if (d.n - d.rpos < 5) return 1;
   if (d.p[d.rpos] & 1) return GS_E_WIRE;  // compressed message: never negotiated
   const size_t mlen = be32(d.p + d.rpos + 1);
   if (d.n - d.rpos - 5 < mlen) return 1;
   *len = mlen;
+  if (borrow) {  // the bytes stay where they were received until the next call on the stream
+    *borrow = d.p + d.rpos + 5;
+    d.rpos += 5 + mlen;
+    return GS_OK;
+  }
   if (mlen > cap || (!out && mlen)) return GS_E_NOSPACE;
   if (mlen) memcpy(out, d.p + d.rpos + 5, mlen);
   d.rpos += 5 + mlen;
@@ -441,9 +447,7 @@ int gs_grpc_client_connect(const char *unix_path, uint32_t timeout_ms, gs_grpc_c
   }
   c->w.fd = fd;
   set_io_timeouts(fd, 30);
-  int sz = 4 << 20;
-  setsockopt(fd, SOL_SOCKET, SO_SNDBUF, &sz, sizeof(sz));
-  setsockopt(fd, SOL_SOCKET, SO_RCVBUF, &sz, sizeof(sz));
+  set_big_buffers(fd, 4 << 20);
   const uint16_t ids[3] = {kSetEnablePush, kSetInitialWindowSize, kSetMaxFrameSize};
   const uint32_t vals[3] = {0, kOurStreamWindow, kOurMaxFrame};
   bool ok = c->w.write_all((const uint8_t *)kPreface, 24) && c->w.send_settings(ids, vals, 3) &&
@@ -521,8 +525,9 @@ int gs_grpc_client_stream_open(gs_grpc_client *c, const char *method_path, const
   return GS_OK;
 }
 
-int gs_grpc_client_stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp, size_t resp_cap,
-                               size_t *resp_len, int32_t *grpc_status, uint32_t timeout_ms) {
+static int stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp, size_t resp_cap,
+                       size_t *resp_len, int32_t *grpc_status, uint32_t timeout_ms,
+                       const uint8_t **borrow) {
   if (!c || !resp_len || !grpc_status) return GS_E_INVAL;
   auto it = c->streams.find(stream);
   if (it == c->streams.end()) return GS_E_NOTFOUND;
@@ -530,7 +535,7 @@ int gs_grpc_client_stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp
   *grpc_status = -1;
   const int64_t deadline = now_ms() + timeout_ms;
   for (;;) {
-    const int t = take_message(s, resp, resp_cap, resp_len);
+    const int t = take_message(s, resp, resp_cap, resp_len, borrow);
     if (t != 1) return t;
     if (s.closed) {  // no further message: the stream's status is the answer
       *grpc_status = s.grpc_status >= 0 ? s.grpc_status : 2;
@@ -547,6 +552,17 @@ int gs_grpc_client_stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp
       return GS_E_STATE;
     }
   }
+}
+
+int gs_grpc_client_stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp, size_t resp_cap,
+                               size_t *resp_len, int32_t *grpc_status, uint32_t timeout_ms) {
+  return stream_next(c, stream, resp, resp_cap, resp_len, grpc_status, timeout_ms, nullptr);
+}
+
+int gs_grpc_client_stream_next_borrow(gs_grpc_client *c, uint32_t stream, const uint8_t **msg,
+                                      size_t *len, int32_t *grpc_status, uint32_t timeout_ms) {
+  if (!msg) return GS_E_INVAL;
+  return stream_next(c, stream, nullptr, 0, len, grpc_status, timeout_ms, msg);
 }
 
 int gs_grpc_client_stream_cancel(gs_grpc_client *c, uint32_t stream) {

@@ -727,9 +727,7 @@ void gs_server::accept_one() {
   const int fd = accept4(listen_fd, nullptr, nullptr, SOCK_CLOEXEC);
   if (fd < 0) return;
   set_io_timeouts(fd, 10);
-  int sz = 4 << 20;  // room for a whole AllocateRequest / a long run of list frames
-  setsockopt(fd, SOL_SOCKET, SO_SNDBUF, &sz, sizeof(sz));
-  setsockopt(fd, SOL_SOCKET, SO_RCVBUF, &sz, sizeof(sz));
+  set_big_buffers(fd, 4 << 20);
   std::unique_ptr<Conn> c(new Conn());
   c->w.fd = fd;
   // server connection preface (RFC 7540 3.5): SETTINGS, then open the connection window
@@ -770,9 +768,12 @@ void gs_server::run() {
     pfds.push_back({wake_fd, POLLIN, 0});
     pfds.push_back({listen_fd, POLLIN, 0});
     for (auto &c : conns) pfds.push_back({c->w.fd, POLLIN, 0});
-    const int r = poll(pfds.data(), (nfds_t)pfds.size(), 1000);
+    const int r = poll(pfds.data(), (nfds_t)pfds.size(), 200);
     if (r < 0 && errno != EINTR) break;
-    if (r <= 0) continue;
+    if (r <= 0) {
+      pump_law();  // a health change nobody announced with gs_plugin_notify_health
+      continue;
+    }
     const size_t n_conns = conns.size();  // accept_one may append
     if (pfds[0].revents & POLLIN) {
       uint64_t v;

@@ -67,6 +67,8 @@ def parse_args(argv=None):
     flag("health-probe-interval", type=int, default=0,
          help="with --probe and --health-check: every N seconds sweep each GPU's free memory (0 = off)")
     boolflag("no-register", "serve without registering with kubelet (harness)")
+    flag("transport", default="native", choices=("native", "grpcio"),
+         help="gRPC transport: the library's own HTTP/2 server (native) or Python grpcio")
     a = ap.parse_args(argv)
     for k in ("mps", "health_check", "query_kubelet", "logtostderr", "probe", "no_register"):
         v = str(getattr(a, k)).lower()
@@ -175,8 +177,11 @@ class PluginInstance:
         self.probe_thread = None
         self._allocate = self.plugin.Allocate
         self.plugin.Allocate = self.allocate_and_probe
-        self.server = DevicePluginServer(
-            self.plugin, os.path.join(a.socket_dir, os.path.basename(SERVER_SOCK)))
+        if a.transport == "native":
+            from .native_transport import NativeDevicePluginServer as server_cls
+        else:
+            server_cls = DevicePluginServer
+        self.server = server_cls(self.plugin, os.path.join(a.socket_dir, os.path.basename(SERVER_SOCK)))
         self.stop = threading.Event()
 
     def allocate_and_probe(self, request):

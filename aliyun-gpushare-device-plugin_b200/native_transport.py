@@ -140,9 +140,6 @@ class NativeClient:
     def __exit__(self, *a):
         self.close()
 
-    def _grow(self, need):
-        self.buf = C.create_string_buffer(max(need, 2 * len(self.buf)))
-
     def call(self, method, request=b"", service=SERVICE):
         """Unary call; returns the response bytes or raises RpcError."""
         path = ("/%s/%s" % (service, method)).encode()
@@ -166,18 +163,14 @@ class NativeClient:
         return sid.value
 
     def next_message(self, sid, timeout_ms=5000, copy=True):
-        """Next message of a server stream: bytes (or its length with copy=False, the bytes
-        staying in self.buf); None when the stream ended OK; RpcError otherwise."""
-        n, status = C.c_size_t(), C.c_int32()
-        while True:
-            rc = self.lib.gs_grpc_client_stream_next(self.h, sid, self.buf, len(self.buf), C.byref(n),
-                                                     C.byref(status), timeout_ms)
-            if rc == L.GS_E_NOSPACE:
-                self._grow(n.value)
-                continue
-            break
+        """Next message of a server stream: bytes (with copy=False an (address, length) pair
+        borrowed from the client until the next call on this stream); None when the stream
+        ended OK; RpcError otherwise."""
+        n, status, ptr = C.c_size_t(), C.c_int32(), C.c_void_p()
+        rc = self.lib.gs_grpc_client_stream_next_borrow(self.h, sid, C.byref(ptr), C.byref(n),
+                                                        C.byref(status), timeout_ms)
         if rc == L.GS_OK:
-            return C.string_at(self.buf, n.value) if copy else n.value
+            return C.string_at(ptr, n.value) if copy else (ptr.value, n.value)
         if rc == L.GS_E_TIMEOUT:
             raise TimeoutError("no message within %d ms" % timeout_ms)
         if rc == L.GS_E_STATE and status.value == 0:

@@ -366,6 +366,11 @@ GS_API int gs_grpc_client_stream_open(gs_grpc_client *c, const char *method_path
 GS_API int gs_grpc_client_stream_next(gs_grpc_client *c, uint32_t stream, uint8_t *resp,
                                       size_t resp_cap, size_t *resp_len,
                                       int32_t *grpc_status, uint32_t timeout_ms);
+/* Same, without the copy: *msg points at the bytes where they were received and
+ * stays valid until the next call on this client.                             */
+GS_API int gs_grpc_client_stream_next_borrow(gs_grpc_client *c, uint32_t stream,
+                                             const uint8_t **msg, size_t *len,
+                                             int32_t *grpc_status, uint32_t timeout_ms);
 GS_API int gs_grpc_client_stream_cancel(gs_grpc_client *c, uint32_t stream);
 GS_API const char *gs_grpc_last_error(void); /* thread-local, valid until the next call */
 

@@ -9,6 +9,7 @@ import tempfile
 import time
 
 import grpc
+import pytest
 
 from gpushare_b200 import daemon
 from gpushare_b200.grpc_harness import KubeletStub
@@ -28,7 +29,8 @@ def test_flag_names_and_defaults_match_reference():
     assert a.memory_unit == "MiB" and a.health_check and not a.query_kubelet and a.mps
 
 
-def test_daemon_config1_end_to_end(golden_cases):
+@pytest.mark.parametrize("transport", ["native", "grpcio"])
+def test_daemon_config1_end_to_end(golden_cases, transport):
     c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
     with tempfile.TemporaryDirectory(prefix="gsd") as d:
         pods = os.path.join(d, "pods.json")
@@ -39,7 +41,7 @@ def test_daemon_config1_end_to_end(golden_cases):
                    PYTHONPATH=ROOT)
         proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "-logtostderr", "--v=5",
                                  "--memory-unit=GiB", "--nvml-lib", FAKE_NVML, "--socket-dir", d,
-                                 "--pod-source-file", pods, "--health-check"],
+                                 "--pod-source-file", pods, "--health-check", "--transport", transport],
                                 env=env, stderr=subprocess.PIPE, text=True)
         try:
             assert kubelet.wait_registered(30), proc.stderr.read() if proc.poll() is not None else ""
