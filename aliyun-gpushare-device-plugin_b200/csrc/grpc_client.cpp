@@ -17,6 +17,7 @@
 #include <memory>
 #include <string>
 #include <unordered_map>
+#include <utility>
 #include <vector>
 
 #include "gpushare.h"
@@ -44,6 +45,12 @@ struct RBuf {  // received message bytes of one stream; never zero-filled
   }
   void compact() {
     if (rpos == n) rpos = n = 0;
+  }
+  void swap(RBuf &o) {
+    std::swap(p, o.p);
+    std::swap(n, o.n);
+    std::swap(cap, o.cap);
+    std::swap(rpos, o.rpos);
   }
 };
 
@@ -103,6 +110,19 @@ struct gs_grpc_client {
   uint8_t cont_flags = 0;
   std::vector<Header> headers;
   std::string last_error;
+  RBuf spare;  // the largest message buffer of a finished stream, handed to the next one:
+               // a 90 MB list does not fault its pages in again on every stream
+
+  void drop_stream(uint32_t id) {
+    auto it = streams.find(id);
+    if (it == streams.end()) return;
+    RBuf &d = it->second->data;
+    if (d.cap > spare.cap) {
+      d.n = d.rpos = 0;
+      spare.swap(d);
+    }
+    streams.erase(it);
+  }
 
   bool fail(const char *what) {
     if (!broken) last_error = what;
@@ -360,6 +380,7 @@ struct gs_grpc_client {
     s->id = next_id;
     next_id += 2;
     s->send_window = peer_initial_window;
+    if (spare.cap) s->data.swap(spare);
     CStream *raw = s.get();
     streams[raw->id] = std::move(s);
     return raw;
@@ -507,7 +528,7 @@ int gs_grpc_client_unary(gs_grpc_client *c, const char *method_path, const uint8
       else if (t != GS_OK) rc = GS_E_WIRE;  // OK status without a complete message
     }
   }
-  c->streams.erase(id);
+  c->drop_stream(id);
   return rc;
 }
 
@@ -518,7 +539,7 @@ int gs_grpc_client_stream_open(gs_grpc_client *c, const char *method_path, const
   if (!s) return GS_E_STATE;
   if (!c->send_request(*s, method_path, req, req_len)) {
     g_last_error = c->last_error;
-    c->streams.erase(s->id);
+    c->drop_stream(s->id);
     return GS_E_STATE;
   }
   *stream = s->id;
@@ -570,7 +591,7 @@ int gs_grpc_client_stream_cancel(gs_grpc_client *c, uint32_t stream) {
   auto it = c->streams.find(stream);
   if (it == c->streams.end()) return GS_E_NOTFOUND;
   if (!it->second->closed && !c->broken) c->w.send_rst(stream, kErrCancel);
-  c->streams.erase(it);
+  c->drop_stream(stream);
   return GS_OK;
 }
 

@@ -35,6 +35,7 @@ using namespace gs_h2;
 
 namespace {
 
+constexpr size_t kMaxStreams = 128;  // advertised in our SETTINGS and enforced
 enum Method { kUnknown, kOptions, kListAndWatch, kAllocate, kPreStart, kPreferred };
 const char kServicePrefix[] = "/v1beta1.DevicePlugin/";
 
@@ -398,6 +399,8 @@ bool gs_server::on_headers_complete(Conn &c, uint32_t id, uint8_t flags) {
   }
   if (id <= c.last_stream) return true;  // headers of a stream already closed: ignore
   c.last_stream = id;
+  if (c.streams.size() >= kMaxStreams)   // SETTINGS_MAX_CONCURRENT_STREAMS, RFC 7540 5.1.2
+    return c.w.send_rst(id, kErrRefused);
   Stream &s = c.streams[id];
   s.id = id;
   s.send_window = c.peer_initial_window;
@@ -725,14 +728,17 @@ void gs_server::drop_conn(Conn &c) {
 
 void gs_server::accept_one() {
   const int fd = accept4(listen_fd, nullptr, nullptr, SOCK_CLOEXEC);
-  if (fd < 0) return;
+  if (fd < 0) {
+    if (errno == EMFILE || errno == ENFILE || errno == ENOMEM) usleep(10000);  // do not spin on poll
+    return;
+  }
   set_io_timeouts(fd, 10);
   set_big_buffers(fd, 4 << 20);
   std::unique_ptr<Conn> c(new Conn());
   c->w.fd = fd;
   // server connection preface (RFC 7540 3.5): SETTINGS, then open the connection window
   const uint16_t ids[3] = {kSetMaxConcurrentStreams, kSetInitialWindowSize, kSetMaxFrameSize};
-  const uint32_t vals[3] = {128, kOurStreamWindow, kOurMaxFrame};
+  const uint32_t vals[3] = {(uint32_t)kMaxStreams, kOurStreamWindow, kOurMaxFrame};
   if (!c->w.send_settings(ids, vals, 3) ||
       !c->w.send_window_update(0, kOurConnWindow - kDefaultWindow)) {
     close(fd);

@@ -364,6 +364,40 @@ def run_ours(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     dt_abi, s_abi = timed(step_abi)
     dt_api, s_api = timed(step_api)
+
+    # third leg (SURVEY 8(d) metric 1(ii)): the same job with kubelet's bytes arriving over the
+    # unix socket -- the library's HTTP/2 + gRPC transport on both ends, the client standing in
+    # for kubelet. The serving thread makes the decision; this thread only queues the sweep.
+    import tempfile
+
+    from gpushare_b200.native_transport import NativeClient, NativeDevicePluginServer
+    sockdir = tempfile.mkdtemp(prefix="gsb")
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "aliyungpushare.sock"))
+    srv.Start()
+    cl = NativeClient(srv.socket)
+    rpc_path = b"/v1beta1.DevicePlugin/Allocate"
+    rn, rstatus, rmsg = C.c_size_t(), C.c_int32(), C.create_string_buffer(128)
+
+    def step_socket(sched):
+        for _ in range(WAVES_PER_STEP):
+            L.check(lib.gs_plugin_set_pods(plug.h, views, len(pods)))
+            for k, w in enumerate(wires):
+                rc = lib.gs_grpc_client_unary(cl.h, rpc_path, w, len(w), resp, 4096, C.byref(rn),
+                                              C.byref(rstatus), rmsg, 128)
+                if rc != 0 or rstatus.value != 0 or rn.value < 100:
+                    raise RuntimeError("Allocate over the socket: rc %d status %d %r" % (
+                        rc, rstatus.value, rmsg.value))
+                sched.grant(*slices[k])
+            sched.pump()
+
+    dt_sock, _s_sock = timed(step_socket)
+    sock_stats = srv.stats()
+    cl.close()
+    srv.Stop()
+    try:
+        os.rmdir(sockdir)
+    except OSError:
+        pass
     clocks = sampler.stop() if sampler else None
 
     # probe kernels alone (device-resident ranges, CUDA events on the probe stream)
@@ -432,6 +466,11 @@ def run_ours(args, rank, world, local_rank):
                     "note": "request and response bytes live on the host (the kubelet side); the GPU "
                             "leg's host->device traffic is the slice descriptors passed as kernel "
                             "parameters, device->host the 32-byte verdict per slice"},
+            "over_socket": {"value": decisions / dt_sock, "unit": "decisions/s",
+                            "transport": "gs_server_* <- unix socket <- gs_grpc_client_* (HTTP/2 + gRPC "
+                                         "in the library on both ends; the client stands in for kubelet)",
+                            "allocate_calls_served_rank0": int(sock_stats["allocate_calls"]),
+                            "request_bytes_per_step": int(req_avg * TENANTS * WAVES_PER_STEP)},
             "gpu_launches": int(la[0]),
             "roofline": {"bound": "hbm", "achieved": live_gbps, "peak": peak, "unit": "GB/s",
                          "frac": live_gbps / peak, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs: "

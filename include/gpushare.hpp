@@ -62,6 +62,7 @@ class NvidiaDevicePlugin {
     }
   }
   ~NvidiaDevicePlugin() {
+    if (server_) gs_server_stop(server_);
     gs_plugin_free(plugin_);
     gs_table_free(table_);
   }
@@ -126,7 +127,42 @@ class NvidiaDevicePlugin {
     check(gs_law_mark_unhealthy_gpu(table_, gpu_or_all), "gs_law_mark_unhealthy_gpu");
     gs_plugin_notify_health(plugin_);
   }
-  void Stop() { gs_plugin_stop(plugin_); }
+  // Start (server.go:114-142): serve the five RPCs on `socket_path` with the library's own
+  // gRPC transport. Serve (server.go:232-249) = Start + Register, undone when Register fails.
+  void Start(const std::string &socket_path = GS_DEVICE_PLUGIN_PATH GS_SERVER_SOCK_NAME,
+             gs_server_allocate_fn allocate = nullptr, void *user = nullptr) {
+    gs_server_config cfg{};
+    cfg.socket_path = socket_path.c_str();
+    cfg.allocate = allocate;
+    cfg.user = user;
+    check(gs_server_start(plugin_, &cfg, &server_), "gs_server_start");
+    socket_ = socket_path;
+  }
+  void Register(const std::string &kubelet_socket = GS_KUBELET_SOCKET,
+                const std::string &resource_name = GS_RESOURCE_NAME) {  // server.go:158-177
+    const size_t slash = socket_.rfind('/');
+    const std::string endpoint = slash == std::string::npos ? socket_ : socket_.substr(slash + 1);
+    check(gs_register(kubelet_socket.c_str(), endpoint.c_str(), resource_name.c_str(), 5000), "Register");
+  }
+  void Serve(const std::string &socket_path = GS_DEVICE_PLUGIN_PATH GS_SERVER_SOCK_NAME,
+             const std::string &kubelet_socket = GS_KUBELET_SOCKET) {
+    Start(socket_path);
+    try {
+      Register(kubelet_socket);
+    } catch (...) {
+      Stop();
+      throw;
+    }
+  }
+  // Stop (server.go:145-155): close(m.stop); a running server ends its streams and goes away
+  void Stop() {
+    if (server_) {
+      gs_server_stop(server_);
+      server_ = nullptr;
+    } else {
+      gs_plugin_stop(plugin_);
+    }
+  }
 
   gs_table *table() const { return table_; }
   gs_plugin *handle() const { return plugin_; }
@@ -134,6 +170,8 @@ class NvidiaDevicePlugin {
  private:
   gs_table *table_ = nullptr;
   gs_plugin *plugin_ = nullptr;
+  gs_server *server_ = nullptr;
+  std::string socket_;
 };
 
 }  // namespace gpushare

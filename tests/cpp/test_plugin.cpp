@@ -1,6 +1,8 @@
 // C++ consumer of include/gpushare.hpp: golden case G1 (binpack-1, BASELINE config 1) and the
 // error response, decoded by hand. Built and run by tests/test_cpp_face.py.
 #include <stdio.h>
+#include <stdlib.h>
+#include <unistd.h>
 #include <string.h>
 
 #include <map>
@@ -94,6 +96,31 @@ int main() {
   bool threw = false;
   try { plugin.Allocate(Bytes{0x0A, 0x05, 0x01}); } catch (const gpushare::Error &err) { threw = err.status == GS_E_WIRE; }
   EXPECT(threw);
+  {  // the transport from C++: Start on a socket, call it with the library's client, Stop
+    std::vector<std::string> one = {uuids[0]};
+    gpushare::NvidiaDevicePlugin served(one, 16384, gpushare::MemoryUnit::GiB, "node-a");
+    char dir[] = "/tmp/gscppXXXXXX";
+    EXPECT(mkdtemp(dir) != nullptr);
+    const std::string sock = std::string(dir) + "/aliyungpushare.sock";
+    served.Start(sock);
+    gs_grpc_client *c = nullptr;
+    EXPECT(gs_grpc_client_connect(sock.c_str(), 5000, &c) == GS_OK);
+    uint8_t resp[1024];
+    size_t n = 0;
+    int32_t status = -1;
+    char msg[64];
+    EXPECT(gs_grpc_client_unary(c, "/v1beta1.DevicePlugin/Allocate", req.data(), req.size(), resp, sizeof(resp),
+                                &n, &status, msg, sizeof(msg)) == GS_OK && status == 0);
+    auto e2 = envs(Bytes(resp, resp + n));  // no pod, one GPU: the UUID fallback (allocate.go:154-180)
+    EXPECT(e2["NVIDIA_VISIBLE_DEVICES"] == uuids[0] && e2["ALIYUN_COM_GPU_MEM_IDX"] == "0");
+    bool refused = false;
+    try { served.Register(std::string(dir) + "/kubelet.sock"); } catch (const gpushare::Error &err) { refused = err.status == GS_E_TIMEOUT; }
+    EXPECT(refused);  // nobody listens there
+    gs_grpc_client_close(c);
+    served.Stop();
+    EXPECT(access(sock.c_str(), F_OK) != 0);
+    rmdir(dir);
+  }
   printf("CPP FACE OK\n");
   return 0;
 }

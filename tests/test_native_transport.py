@@ -320,6 +320,33 @@ def test_server_rejects_garbage_and_survives(golden_cases, sockdir):
         srv.Stop()
 
 
+def test_stream_cap_is_enforced(golden_cases, sockdir):
+    """SETTINGS_MAX_CONCURRENT_STREAMS (128) is advertised and enforced: the 129th open watch
+    stream is refused with RST_STREAM, the others and the connection are untouched."""
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    try:
+        with NativeClient(srv.socket) as cl:
+            healthy = table.payload_size()
+            sids = [cl.open_stream("ListAndWatch") for _ in range(128)]
+            for sid in sids:
+                assert len(cl.next_message(sid)) == healthy
+            extra = cl.open_stream("ListAndWatch")
+            with pytest.raises(RpcError) as e:
+                cl.next_message(extra)
+            assert e.value.code == 13                      # reset by the peer: REFUSED_STREAM
+            cl.cancel(sids[0])
+            again = cl.open_stream("ListAndWatch")         # a slot is free again
+            assert len(cl.next_message(again)) == healthy
+            plug.unhealthy(2)
+            for sid in sids[1:] + [again]:                 # every watcher gets the one re-send
+                assert len(cl.next_message(sid)) == healthy + 2 * 16
+    finally:
+        srv.Stop()
+
+
 def test_abi_argument_checks(sockdir):
     lib = L.load()
     import ctypes as C
@@ -335,3 +362,31 @@ def test_abi_argument_checks(sockdir):
     cfg = L.ServerConfig()
     cfg.socket_path = os.path.join(sockdir, "no", "such", "dir", "s.sock").encode()
     assert lib.gs_server_start(plug.h, C.byref(cfg), C.byref(h)) == L.GS_E_STATE
+
+
+def _build_transport_test(tmp_path, name, sanitize):
+    exe = str(tmp_path / name)
+    srcs = [os.path.join(CSRC, f) for f in ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp",
+                                             "grpc_server.cpp", "grpc_client.cpp")]
+    subprocess.run(["g++", "-std=c++17", "-O1", "-g"] + sanitize + ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC,
+                   os.path.join(ROOT, "tests", "cpp", "fuzz_transport.cpp")] + srcs + ["-o", exe, "-lpthread"],
+                   check=True)
+    return exe
+
+
+def test_transport_fuzz_under_address_and_ub_sanitizers(tmp_path):
+    """4000 mutated client sessions against a live server and 1000 mutated server sessions
+    against the client, ASan + UBSan, with well-formed calls checked in between."""
+    exe = _build_transport_test(tmp_path, "fuzz_transport",
+                                ["-fsanitize=address,undefined", "-fno-sanitize-recover=all"])
+    out = subprocess.run([exe, "fuzz", "4000"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "TRANSPORT FUZZ OK" in out.stdout, (out.stdout + out.stderr)[-3000:]
+
+
+def test_transport_under_thread_sanitizer(tmp_path):
+    """Two Allocate callers, a ListAndWatch reader, a health marker and Stop at once: no race,
+    and the watch stream ends with status OK."""
+    exe = _build_transport_test(tmp_path, "race_transport", ["-fsanitize=thread"])
+    out = subprocess.run([exe, "race", "2"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "TRANSPORT RACE OK" in out.stdout \
+        and "WARNING: ThreadSanitizer" not in out.stderr, (out.stdout + out.stderr)[-4000:]

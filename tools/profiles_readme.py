@@ -16,9 +16,12 @@ for n in (1, 2, 4, 8):
                  d["roofline"]["kernels"]["verify_gbps"], d["roofline"]["alone"]["combined_gbps"]))
 ref = load("r01_bench_reference_1gpu.json")["value"]
 L200 = load("r01_bench_1gpu_200steps.json")
+LD = load("r01_bench_1gpu_default.json")
+RD = load("r01_bench_reference_1gpu_default.json")
 sw = load("r01_allocate_sweep.json")["rows"]
 co = load("r01_colocation_8gpu.json")
-h = load("r01_harness_8gpu.json")
+h = load("r01_harness_8gpu_native.json")
+hg = load("r01_harness_8gpu_grpcio.json")
 md = """# profiles/ -- round 1 evidence
 
 All numbers from B200 boxes via `gpurun` (driver 580.159, CUDA 12.9), never under a profiler unless the
@@ -40,6 +43,12 @@ A 200-step run of the same command (`r01_bench_1gpu_200steps.json`, timed region
 end-of-run drain of the in-flight sweep is amortised and the board sits at its power cap): %.0f decisions/s at the
 C ABI, %.0f through the public API, probe %.0f GB/s in step.
 
+The default command (`python bench.py`: 100 steps, W=3) on another box, with the over-the-socket leg
+(`r01_bench_1gpu_default.json`, `r01_bench_reference_1gpu_default.json`): %.0f decisions/s at the C ABI, %.0f through the
+public API, **%.0f with kubelet's bytes arriving over the unix socket** (library transport on both ends, %.1f GB/s of
+request bytes through the socket), probe %.0f GB/s in step; reference model %.0f on that box => %.1fx end to end,
+%.1fx over the socket.
+
 Reference model on the 1-GPU call's box, one thread (`r01_bench_reference_1gpu.json`): **%.0f decisions/s**
 => %.1fx at 1 GPU (e2e / reference).
 
@@ -47,7 +56,10 @@ Reference model on the 1-GPU call's box, one thread (`r01_bench_reference_1gpu.j
 
 | ids per request | pods in list | this library /s | reference model /s | ratio | request bytes scanned |
 |---:|---:|---:|---:|---:|---:|
-""" % (L200["value"], L200["e2e"]["value"], L200["roofline"]["achieved"], ref, rows[0][2] / ref)
+""" % (L200["value"], L200["e2e"]["value"], L200["roofline"]["achieved"],
+       LD["value"], LD["e2e"]["value"], LD["over_socket"]["value"],
+       LD["over_socket"]["value"] * LD["config"]["request_bytes_avg"] / 1e9, LD["roofline"]["achieved"], RD["value"],
+       LD["e2e"]["value"] / RD["value"], LD["over_socket"]["value"] / RD["value"], ref, rows[0][2] / ref)
 for r in sw:
     md += "| %d | %d | %.0f | %.0f | %.1fx | %.1f GB/s |\n" % (
         r["ids"], r["pods"], r["ours_per_s"], r["reference_model_per_s"], r["ratio"], r["ours_request_gbps"])
@@ -59,16 +71,21 @@ Every tenant allocated through the C ABI, all granted ranges (%.0f GiB) swept co
 process: per-GPU combined %.0f-%.0f GB/s, aggregate %.1f TB/s by wall clock; the one corrupted tenant (%d) was the only
 one reported (%s).
 
-## Host-side metrics, 8 GPUs' worth (`r01_harness_8gpu.json`)
+## Host-side metrics over the unix socket, 8 GPUs' worth (`r01_harness_8gpu_native.json`, `..._grpcio.json`)
+
+Both ends of the socket are the library's own HTTP/2 + gRPC transport ("native": `gs_server_*` serving,
+`gs_grpc_client_*` standing in for kubelet) or grpc-core driven from Python on both ends ("grpcio"), same box, same run.
 
 * device table build %.0f ms (reference model getDevices %.0f ms); payload %.1f MB
-* ListAndWatch stream open -> last byte at the client: %.0f ms median (Python grpcio)
-* XID -> re-advertised full list at the client, Allocate loop running: p50 %.0f ms, p99 %.0f ms; one re-send per event
-  (the reference design re-sends once per fake device: %d x %.0f ms of marshal each, by arithmetic)
-* Allocate over the unix-socket gRPC harness: %.0f decisions/s at 1 024 ids, %.0f at 40 960 ids
+* ListAndWatch stream open -> last byte at the client: %.1f ms median native, %.0f ms grpcio
+* XID -> re-advertised full list at the client, Allocate loop running: p50 %.1f ms, p99 %.1f ms native
+  (%.0f / %.0f ms grpcio); one re-send per event (the reference design re-sends once per fake device:
+  %d x %.0f ms of marshal each, by arithmetic)
+* Allocate over the socket: %.0f decisions/s at 2 ids, %.0f at 1 024 ids, %.0f at 40 960 ids (2 MB requests) native;
+  %.0f / %.0f / %.0f grpcio
 
-| GPUs' worth of ids | payload | table build | ListAndWatch open -> last byte (median) | XID -> re-advertised list p50 / p99 | Allocate over gRPC, 1 024 ids |
-|---:|---:|---:|---:|---:|---:|
+| transport | GPUs' worth of ids | payload | table build | ListAndWatch open -> last byte (median) | XID -> re-advertised list p50 / p99 | Allocate over the socket: 2 / 1 024 / 40 960 ids | Allocate under health churn |
+|---|---:|---:|---:|---:|---:|---:|---:|
 %s
 ## Kernel evidence
 
@@ -78,13 +95,20 @@ one reported (%s).
        max(p["combined_gbps"] for p in pg), co["probe"]["aggregate_gbps_wall"] / 1000,
        co["fault_injection"]["victim_tenant"], co["fault_injection"]["flagged_tenants"],
        h["table_build_ms"], h["reference_model"]["get_devices_ms"], h["payload_bytes"] / 1e6,
-       h["law_open_to_last_byte_ms"]["median"], h["health_readvertise_ms"]["p50"], h["health_readvertise_ms"]["p99"],
+       h["law_open_to_last_byte_ms"]["median"], hg["law_open_to_last_byte_ms"]["median"],
+       h["health_readvertise_ms"]["p50"], h["health_readvertise_ms"]["p99"],
+       hg["health_readvertise_ms"]["p50"], hg["health_readvertise_ms"]["p99"],
        h["reference_model"]["resends_per_gpu_event_by_design"], h["reference_model"]["marshal_per_send_ms"],
-       h["allocate_over_grpc"]["1024"]["decisions_per_s"], h["allocate_over_grpc"]["40960"]["decisions_per_s"],
-       "".join("| %d | %.1f MB | %.1f ms | %.0f ms | %.0f / %.0f ms | %.0f /s |\n" % (
-           n, x["payload_bytes"] / 1e6, x["table_build_ms"], x["law_open_to_last_byte_ms"]["median"],
+       h["allocate_over_grpc"]["2"]["decisions_per_s"], h["allocate_over_grpc"]["1024"]["decisions_per_s"],
+       h["allocate_over_grpc"]["40960"]["decisions_per_s"],
+       hg["allocate_over_grpc"]["2"]["decisions_per_s"], hg["allocate_over_grpc"]["1024"]["decisions_per_s"],
+       hg["allocate_over_grpc"]["40960"]["decisions_per_s"],
+       "".join("| %s | %d | %.1f MB | %.1f ms | %.1f ms | %.1f / %.1f ms | %.0f / %.0f / %.0f /s | %.0f /s |\n" % (
+           t, n, x["payload_bytes"] / 1e6, x["table_build_ms"], x["law_open_to_last_byte_ms"]["median"],
            x["health_readvertise_ms"]["p50"], x["health_readvertise_ms"]["p99"],
-           x["allocate_over_grpc"]["1024"]["decisions_per_s"])
-           for n, x in ((n, load("r01_harness_%dgpu.json" % n)) for n in (1, 2, 4, 8))))
+           x["allocate_over_grpc"]["2"]["decisions_per_s"], x["allocate_over_grpc"]["1024"]["decisions_per_s"],
+           x["allocate_over_grpc"]["40960"]["decisions_per_s"], x["allocate_under_churn_per_s"])
+           for t, n, x in ((t, n, load("r01_harness_%dgpu_%s.json" % (n, t)))
+                           for t in ("native", "grpcio") for n in (1, 2, 4, 8))))
 open(os.path.join(P, "README.md"), "w").write(md)
 print(md[:1600])
