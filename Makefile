@@ -19,7 +19,9 @@ OBJS      := $(CPP_SRCS:.cpp=.o) $(CU_SRCS:.cu=.o)
 ORACLE_SO := oracle/libgs_oracle.so
 FAKE_NVML := tests/fake_nvml/libfake_nvml.so
 
-all: $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML)
+DAEMON    := $(PKG)/bin/gpushare-device-plugin-v2
+
+all: $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON)
 
 $(CSRC)/%.o: $(CSRC)/%.cpp include/gpushare.h $(wildcard $(CSRC)/*.h)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
@@ -29,6 +31,12 @@ $(CSRC)/%.o: $(CSRC)/%.cu include/gpushare.h $(wildcard $(CSRC)/*.h)
 
 $(CORE_SO): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -ldl -lpthread
+
+# The node daemon as a native binary (flags, kube I/O over OpenSSL, supervisor loop) over the core library.
+$(DAEMON): $(wildcard $(PKG)/daemon_cpp/*.cpp $(PKG)/daemon_cpp/*.h) include/gpushare.h $(CORE_SO)
+	mkdir -p $(PKG)/bin
+	$(CXX) -O2 -g -std=c++17 -Wall -Wextra -Iinclude -I$(PKG)/daemon_cpp $(PKG)/daemon_cpp/main.cpp -o $@ \
+		-L$(PKG) -lgpushare_core -Wl,-rpath,'$$ORIGIN/..' -lssl -lcrypto -lpthread
 
 # Oracle: CPU restatement used ONLY by tests/, smoke() and bench.py's cpu_baseline leg.
 ORACLE_OBJS := $(patsubst %.c,%.o,$(wildcard oracle/*.c)) $(patsubst %.cpp,%.o,$(wildcard oracle/*.cpp))
@@ -43,7 +51,7 @@ $(FAKE_NVML): tests/fake_nvml/fake_nvml.c
 	$(CC) $(CFLAGS) -shared -o $@ $< -lpthread
 
 clean:
-	rm -f $(OBJS) $(CORE_SO) $(ORACLE_OBJS) $(ORACLE_SO) $(FAKE_NVML)
+	rm -f $(OBJS) $(CORE_SO) $(ORACLE_OBJS) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON)
 
 test: all
 	python -m pytest tests -q -m "not gpu"

@@ -1,0 +1,600 @@
+// gpushare-device-plugin-v2 -- the node daemon as one native binary over libgpushare_core.so.
+//
+// Replaces, with the same flags, exit codes and restart behaviour:
+//   cmd/nvidia/main.go:15-78            flags, memory unit, kubelet client, manager
+//   pkg/gpu/nvidia/gpumanager.go:33-111 NVML, FS/OS watchers, the restart loop
+//   pkg/gpu/nvidia/watchers.go, coredump.go
+//   pkg/gpu/nvidia/server.go:43-78      NewNvidiaDevicePlugin (gpu-count patch, cGPU label)
+//   pkg/gpu/nvidia/allocate.go:60-152   list -> decide -> patch under one lock
+// The decision, the device table, the wire format, the gRPC transport and the probe are the
+// library's (include/gpushare.h); this file is flags, I/O and lifecycle. The same program
+// exists in Python (daemon.py); tests run both against the same fake kubelet and cluster.
+#include <execinfo.h>
+#include <limits.h>
+#include <poll.h>
+#include <signal.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/inotify.h>
+#include <time.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "gpushare.h"
+#include "k8s.h"
+
+using namespace gsd;
+
+namespace {
+
+// ---- flags: Go's flag package (main.go:15-26) ------------------------------------------------
+struct Flags {
+  bool mps = false, health_check = false, query_kubelet = false, logtostderr = false;
+  std::string memory_unit = "GiB", kubelet_address = "0.0.0.0", client_cert, client_key, token;
+  long kubelet_port = 10250, timeout = 10, v = 0;
+  // additions (not in the reference)
+  std::string pod_source_file, nvml_lib, socket_dir = "/var/lib/kubelet/device-plugins", transport = "native";
+  bool probe = false, no_register = false;
+  long health_probe_interval = 0;
+};
+
+int g_v = 0;
+void logv(int level, const char *fmt, ...) {
+  if (g_v < level) return;
+  va_list ap;
+  va_start(ap, fmt);
+  vfprintf(stderr, fmt, ap);
+  va_end(ap);
+  fputc('\n', stderr);
+  fflush(stderr);
+}
+
+[[noreturn]] void usage_error(const std::string &msg) {
+  fprintf(stderr, "%s\nUsage of gpushare-device-plugin-v2: see cmd/nvidia/main.go:15-26 for the flags\n",
+          msg.c_str());
+  exit(2);  // Go's flag.ExitOnError
+}
+
+bool parse_bool(const std::string &s, bool &out) {  // strconv.ParseBool
+  if (s == "1" || s == "t" || s == "T" || s == "true" || s == "TRUE" || s == "True") return out = true, true;
+  if (s == "0" || s == "f" || s == "F" || s == "false" || s == "FALSE" || s == "False") return out = false, true;
+  return false;
+}
+
+Flags parse_flags(int argc, char **argv) {
+  Flags f;
+  std::map<std::string, bool *> bools = {{"mps", &f.mps}, {"health-check", &f.health_check},
+                                         {"query-kubelet", &f.query_kubelet}, {"logtostderr", &f.logtostderr},
+                                         {"probe", &f.probe}, {"no-register", &f.no_register}};
+  std::map<std::string, std::string *> strs = {{"memory-unit", &f.memory_unit}, {"kubelet-address", &f.kubelet_address},
+                                               {"client-cert", &f.client_cert}, {"client-key", &f.client_key},
+                                               {"token", &f.token}, {"pod-source-file", &f.pod_source_file},
+                                               {"nvml-lib", &f.nvml_lib}, {"socket-dir", &f.socket_dir},
+                                               {"transport", &f.transport}};
+  std::map<std::string, long *> ints = {{"kubelet-port", &f.kubelet_port}, {"timeout", &f.timeout}, {"v", &f.v},
+                                        {"health-probe-interval", &f.health_probe_interval}};
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i];
+    if (a.size() < 2 || a[0] != '-') break;  // first non-flag argument ends parsing
+    if (a == "--") break;
+    a = a.substr(a[1] == '-' ? 2 : 1);
+    std::string val;
+    bool has_val = false;
+    const size_t eq = a.find('=');
+    if (eq != std::string::npos) {
+      val = a.substr(eq + 1);
+      a.resize(eq);
+      has_val = true;
+    }
+    if (bools.count(a)) {
+      bool b = true;
+      if (has_val && !parse_bool(val, b)) usage_error("invalid boolean value \"" + val + "\" for -" + a);
+      *bools[a] = b;
+      continue;
+    }
+    if (!strs.count(a) && !ints.count(a)) usage_error("flag provided but not defined: -" + a);
+    if (!has_val) {
+      if (i + 1 >= argc) usage_error("flag needs an argument: -" + a);
+      val = argv[++i];
+    }
+    if (strs.count(a)) {
+      *strs[a] = val;
+    } else {
+      char *end = nullptr;
+      const long n = strtol(val.c_str(), &end, 10);
+      if (val.empty() || *end) usage_error("invalid value \"" + val + "\" for flag -" + a);
+      *ints[a] = n;
+    }
+  }
+  if (f.transport != "native") usage_error("this binary serves over the library's own transport only (-transport=native)");
+  return f;
+}
+
+// ---- the slice probe beside Allocate (no counterpart in the reference) --------------------------
+// One worker owns every CUDA call: a grant is swept after its answer left, never before.
+struct ProbeJob {
+  int gpu;
+  uint64_t bytes;
+  int32_t pod_index;
+};
+
+struct ProbeWorker {
+  std::map<int, gs_probe *> probes;  // NVML index -> engine
+  std::map<int, void *> arenas;
+  std::map<int, bool> inflight;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<ProbeJob> queue;
+  std::atomic<bool> stop{false};
+  std::thread th;
+  gs_table *table = nullptr;
+  gs_plugin *plugin = nullptr;
+  long health_interval = 0;
+
+  void mark_bad(int gpu) {
+    gs_law_mark_unhealthy_gpu(table, gpu);
+    gs_plugin_notify_health(plugin);
+  }
+  void harvest(int gpu, bool block) {
+    if (!inflight[gpu]) return;
+    gs_probe *p = probes[gpu];
+    if (!block && gs_probe_poll(p) != GS_OK) return;
+    gs_slice_result r;
+    gs_probe_timing tm;
+    if (gs_probe_wait(p, &r, 1, &tm) == GS_OK) {
+      const double ms = tm.write_ms + tm.verify_ms + tm.scrub_ms;
+      logv(1, "probe: gpu %d swept %llu bytes at %.0f GB/s, %llu mismatching words", gpu,
+           (unsigned long long)tm.bytes, ms > 0 ? 2.0 * (double)tm.bytes / ms / 1e6 : 0.0,
+           (unsigned long long)r.mismatches);
+      if (r.mismatches) mark_bad(gpu);
+    }
+    inflight[gpu] = false;
+  }
+  void start(const ProbeJob &j) {
+    gs_probe *p = probes[j.gpu];
+    harvest(j.gpu, true);  // one arena per GPU: finish the previous sweep
+    if (arenas.count(j.gpu)) {
+      gs_probe_mem_free(p, arenas[j.gpu]);
+      arenas.erase(j.gpu);
+    }
+    uint64_t free_b = 0, total_b = 0;
+    if (gs_probe_mem_info(p, &free_b, &total_b) != GS_OK) return;
+    uint64_t n = j.bytes;  // exactly the granted range, capped by what is free right now
+    const uint64_t room = free_b > (1ull << 30) ? free_b - (1ull << 30) : 0;
+    if (n > room) n = room;
+    n &= ~0xFFFFFull;
+    if (!n) return;
+    void *d = nullptr;
+    if (gs_probe_mem_alloc(p, n, &d) != GS_OK) {
+      logv(1, "probe skipped: %s", gs_cuda_last_error());
+      return;
+    }
+    arenas[j.gpu] = d;
+    gs_slice s;
+    memset(&s, 0, sizeof(s));
+    s.base = d;
+    s.bytes = n;
+    s.seed = (uint32_t)j.pod_index;
+    s.tag = (uint32_t)j.pod_index;
+    uint32_t passes = GS_PROBE_WRITE | GS_PROBE_VERIFY;
+    if (n < (512ull << 20)) passes |= GS_PROBE_SCRUB;
+    if (gs_probe_submit(p, &s, 1, passes) == GS_OK) {
+      inflight[j.gpu] = true;
+      logv(1, "probe: gpu %d, %llu bytes granted to pod %d queued for a sweep", j.gpu, (unsigned long long)n,
+           j.pod_index);
+    }
+  }
+  // health-time probe: what is free on each idle GPU right now, minus a margin
+  void health_sweep() {
+    for (auto &kv : probes) {
+      if (inflight[kv.first]) continue;
+      uint64_t free_b = 0, total_b = 0;
+      if (gs_probe_mem_info(kv.second, &free_b, &total_b) != GS_OK || free_b < (3ull << 30)) continue;
+      ProbeJob j{kv.first, free_b - (2ull << 30), 0x5eed};
+      start(j);
+      harvest(kv.first, true);
+      if (arenas.count(kv.first)) {
+        gs_probe_mem_free(kv.second, arenas[kv.first]);
+        arenas.erase(kv.first);
+      }
+    }
+  }
+  void run() {
+    time_t last = time(nullptr);
+    while (!stop.load()) {
+      ProbeJob j{-1, 0, 0};
+      {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait_for(lk, std::chrono::milliseconds(200), [&] { return stop.load() || !queue.empty(); });
+        if (!queue.empty()) {
+          j = queue.front();
+          queue.pop_front();
+        }
+      }
+      if (j.gpu >= 0 && probes.count(j.gpu)) start(j);
+      for (auto &kv : probes) harvest(kv.first, false);
+      if (health_interval > 0 && time(nullptr) - last >= health_interval) {
+        last = time(nullptr);
+        health_sweep();
+      }
+    }
+    for (auto &kv : probes) {
+      harvest(kv.first, true);
+      if (arenas.count(kv.first)) gs_probe_mem_free(kv.second, arenas[kv.first]);
+      gs_probe_close(kv.second);
+    }
+  }
+  void push(const ProbeJob &j) {
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      queue.push_back(j);
+    }
+    cv.notify_one();
+  }
+};
+
+// ---- one NewNvidiaDevicePlugin + Serve (gpumanager.go:70-79): what a restart rebuilds ------------
+struct PluginInstance {
+  const Flags &f;
+  std::string node;
+  int unit;
+  std::vector<gs_gpu_info> infos;
+  gs_table *table = nullptr;
+  gs_plugin *plugin = nullptr;
+  gs_server *server = nullptr;
+  std::string socket_path, kubelet_socket;
+  bool cluster = false;
+  bool cgpu_disable = false;
+  Transport transport;
+  PodLister lister;
+  std::mutex lock;  // m.Lock(), allocate.go:60
+  std::vector<Pod> pods;
+  std::vector<gs_pod_view> views;
+  std::unique_ptr<ProbeWorker> probes;
+  uint64_t unit_bytes;
+  std::thread health_thread;
+  std::atomic<bool> stop{false};
+  bool health_open = false;
+
+  PluginInstance(const Flags &flags, const std::string &node_name, int mem_unit)
+      : f(flags), node(node_name), unit(mem_unit), unit_bytes(mem_unit == GS_UNIT_MIB ? 1ull << 20 : 1ull << 30) {}
+
+  // getDevices + NewNvidiaDevicePlugin (nvidia.go:50-86, server.go:43-78); exit code 1 on failure
+  bool init(std::string &err) {
+    uint32_t n = 0;
+    if (gs_nvml_device_count(&n) != GS_OK) {
+      err = std::string("nvml: ") + gs_nvml_last_error();
+      return false;
+    }
+    infos.resize(n);
+    for (uint32_t i = 0; i < n; ++i)
+      if (gs_nvml_device_info(i, &infos[i]) != GS_OK) {
+        err = std::string("nvml: ") + gs_nvml_last_error();
+        return false;
+      }
+    if (gs_table_build_from_gpus(infos.data(), n, unit, &table) != GS_OK) {
+      err = "cannot build the device table";
+      return false;
+    }
+    socket_path = f.socket_dir + "/" GS_SERVER_SOCK_NAME;
+    kubelet_socket = f.socket_dir + "/kubelet.sock";
+    if (f.pod_source_file.empty()) {
+      cluster = true;
+      std::string token = f.token;
+      if (f.client_cert.empty() && f.client_key.empty() && token.empty()) {  // main.go:28-36
+        if (!read_file(std::string(kSaDir) + "/token", token)) {
+          fprintf(stderr, "in cluster mode, find token failed, error: open %s/token: no such file or directory\n",
+                  kSaDir);
+          exit(1);
+        }
+      }
+      if (!ApiConfig::load(transport.api, err)) return false;
+      char url[320];
+      snprintf(url, sizeof(url), "https://%s:%ld", f.kubelet_address.c_str(), f.kubelet_port);
+      transport.kubelet_url = url;
+      transport.kubelet_token = token;
+      transport.kubelet_tls.insecure = true;  // main.go:41
+      transport.kubelet_tls.cert_file = f.client_cert;
+      transport.kubelet_tls.key_file = f.client_key;
+      transport.timeout_s = (double)f.timeout;
+      if (const char *u = getenv("GS_KUBELET_URL")) transport.kubelet_url = u;  // tests: a plain-http kubelet
+      if (!patch_gpu_count(transport, node, (int)n, err)) return false;              // server.go:57-60
+      if (!disable_cgpu_isolation_or_not(transport, node, cgpu_disable, err)) return false;  // :61-64
+      lister.t = &transport;
+      lister.node_name = node;
+      lister.query_kubelet = f.query_kubelet;
+    }
+    if (gs_plugin_new(table, node.data(), node.size(), cgpu_disable ? 1 : 0, &plugin) != GS_OK) {
+      err = "cannot create the plugin";
+      return false;
+    }
+    if (f.probe) {
+      std::vector<gs_gpu_info> mapped = infos;
+      if (gs_cuda_map_ordinals(mapped.data(), (uint32_t)mapped.size()) == GS_OK) {
+        probes.reset(new ProbeWorker());
+        probes->table = table;
+        probes->plugin = plugin;
+        probes->health_interval = f.health_check ? f.health_probe_interval : 0;
+        for (const gs_gpu_info &g : mapped) {
+          gs_probe *p = nullptr;
+          if (g.cuda_ordinal >= 0 && gs_probe_open(g.cuda_ordinal, &p) == GS_OK) probes->probes[g.nvml_index] = p;
+        }
+      } else {
+        logv(1, "probe disabled: %s", gs_cuda_last_error());
+      }
+    }
+    return true;
+  }
+
+  bool load_pod_file(std::string &err) {
+    std::string text;
+    JVal doc;
+    if (!read_file(f.pod_source_file, text) || !json_parse(text, doc)) {
+      err = "cannot read " + f.pod_source_file;
+      return false;
+    }
+    const JVal *items = doc.type == JVal::Arr ? &doc : doc.get("items");
+    pods.clear();
+    if (items && items->type == JVal::Arr)
+      for (const JVal &p : items->arr) {
+        pods.emplace_back();
+        if (!pod_from_json(p, pods.back(), err)) return false;
+      }
+    return true;
+  }
+
+  // Allocate (allocate.go:43-201) with this daemon's pod source; runs on the serving thread
+  int allocate(const uint8_t *req, size_t req_len, uint8_t *resp, size_t cap, size_t *resp_len) {
+    std::lock_guard<std::mutex> lk(lock);
+    gs_alloc_result res;
+    memset(&res, 0, sizeof(res));
+    int rc;
+    if (!cluster) {
+      std::string err;
+      if (load_pod_file(err)) {  // re-read per Allocate, like a LIST
+        pod_views(pods, views);
+        gs_plugin_set_pods(plugin, views.data(), views.size());
+      }
+      rc = gs_plugin_allocate(plugin, req, req_len, resp, cap, &res);
+    } else {
+      gs_alloc_ctx ctx;
+      memset(&ctx, 0, sizeof(ctx));
+      ctx.table = table;
+      ctx.node_name = gs_str{node.data(), node.size()};
+      ctx.disable_cgpu_isolation = cgpu_disable ? 1 : 0;
+      struct timespec ts;
+      clock_gettime(CLOCK_REALTIME, &ts);
+      ctx.now_unix_nano = (int64_t)ts.tv_sec * 1000000000ll + ts.tv_nsec;
+      std::string err;
+      if (!lister.list(pods, err)) {  // allocate.go:64-67
+        logv(1, "invalid allocation requst: Failed to find candidate pods due to %s", err.c_str());
+        rc = gs_allocate_error_response(&ctx, req, req_len, GS_ALLOC_ERR_PODS, resp, cap, &res);
+      } else {
+        pod_views(pods, views);
+        char patch[256];
+        rc = gs_allocate(&ctx, req, req_len, views.data(), views.size(), resp, cap, patch, sizeof(patch), &res);
+        if (rc == GS_OK && res.kind == GS_ALLOC_MATCHED) {
+          const Pod &p = pods[(size_t)res.pod_index];
+          if (!patch_pod_assigned(transport, p.ns, p.name, std::string(patch, res.patch_len), err)) {
+            logv(1, "Failed due to %s", err.c_str());  // allocate.go:138-151
+            rc = gs_allocate_error_response(&ctx, req, req_len, GS_ALLOC_ERR_PATCH, resp, cap, &res);
+          }
+        }
+      }
+    }
+    *resp_len = res.resp_len;
+    if (rc == GS_OK && res.kind == GS_ALLOC_MATCHED && probes && probes->probes.count(res.gpu_index))
+      probes->push(ProbeJob{res.gpu_index, res.pod_req_units * unit_bytes, res.pod_index});
+    return rc;
+  }
+  static int allocate_cb(void *user, const uint8_t *req, size_t req_len, uint8_t *resp, size_t cap,
+                         size_t *resp_len) {
+    return static_cast<PluginInstance *>(user)->allocate(req, req_len, resp, cap, resp_len);
+  }
+
+  // Serve (server.go:232-249) + healthcheck (server.go:211-229)
+  bool serve(std::string &err) {
+    gs_server_config cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.socket_path = socket_path.c_str();
+    cfg.allocate = &PluginInstance::allocate_cb;
+    cfg.user = this;
+    const int rc = gs_server_start(plugin, &cfg, &server);
+    if (rc != GS_OK) {
+      err = std::string("could not start device plugin: ") + gs_strerror(rc);
+      return false;
+    }
+    logv(1, "Starting to serve on %s", socket_path.c_str());
+    if (!f.no_register) {
+      const int rr = gs_register(kubelet_socket.c_str(), GS_SERVER_SOCK_NAME, GS_RESOURCE_NAME, 5000);
+      if (rr != GS_OK) {
+        err = std::string("Could not register device plugin: ") + gs_grpc_last_error();
+        gs_server_stop(server);
+        server = nullptr;
+        return false;
+      }
+      logv(1, "Registered device plugin with Kubelet");
+    }
+    if (probes) probes->th = std::thread([this] { probes->run(); });
+    if (f.health_check) {
+      uint64_t bad_mask = 0;
+      if (gs_health_open(&bad_mask) == GS_OK) {
+        health_open = true;
+        for (size_t g = 0; g < infos.size(); ++g)
+          if (bad_mask >> g & 1) {  // nvidia.go:107-111
+            gs_law_mark_unhealthy_gpu(table, (int32_t)g);
+            gs_plugin_notify_health(plugin);
+          }
+        health_thread = std::thread([this] {
+          while (!stop.load()) {
+            gs_health_event ev;
+            if (gs_health_wait(1000, &ev) == GS_OK && !ev.ignored) {
+              gs_law_mark_unhealthy_gpu(table, ev.gpu_index);
+              gs_plugin_notify_health(plugin);
+            }
+          }
+        });
+      }
+    }
+    return true;
+  }
+
+  void shutdown() {  // Stop (server.go:145-155)
+    stop.store(true);
+    if (server) {
+      gs_server_stop(server);
+      server = nullptr;
+    }
+    if (health_thread.joinable()) health_thread.join();
+    if (health_open) gs_health_close();
+    if (probes) {
+      probes->stop.store(true);
+      probes->cv.notify_all();
+      if (probes->th.joinable()) probes->th.join();
+      else
+        for (auto &kv : probes->probes) gs_probe_close(kv.second);
+      probes.reset();
+    }
+    if (plugin) gs_plugin_free(plugin);
+    if (table) gs_table_free(table);
+    plugin = nullptr;
+    table = nullptr;
+  }
+};
+
+// coredump.go:10-30, for this process: the stack of the supervising thread
+void coredump(const std::string &path) {
+  FILE *fp = fopen(path.c_str(), "w");
+  if (!fp) {
+    fprintf(stderr, "failed to write %s: %s\n", path.c_str(), strerror(errno));
+    return;
+  }
+  void *frames[64];
+  const int n = backtrace(frames, 64);
+  fflush(fp);
+  backtrace_symbols_fd(frames, n, fileno(fp));
+  fclose(fp);
+}
+
+int g_sig_pipe[2] = {-1, -1};
+void on_signal(int signum) {
+  const unsigned char b = (unsigned char)signum;
+  if (write(g_sig_pipe[1], &b, 1) < 0) {
+  }
+}
+
+[[noreturn]] void wait_forever() {  // select {} (gpumanager.go:39,46)
+  for (;;) pause();
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+  const Flags f = parse_flags(argc, argv);
+  g_v = (int)f.v;
+  int unit = GS_UNIT_GIB, warned = 0;
+  gs_translate_memory_unit(f.memory_unit.data(), f.memory_unit.size(), &unit, &warned);  // main.go:67-78
+  if (warned) logv(0, "Unsupported memory unit: %s, use memoryUnit Gi as default", f.memory_unit.c_str());
+  const char *node_env = getenv("NODE_NAME");
+  if (!node_env || !*node_env) {
+    fprintf(stderr, "Please set env NODE_NAME\n");  // podmanager.go:55-58
+    return 1;
+  }
+  const std::string node = node_env;
+  logv(1, "Start gpushare device plugin");
+  // ---- sharedGPUManager.Run (gpumanager.go:33-111) ----------------------------------------
+  logv(1, "Loading NVML");
+  if (gs_nvml_open(f.nvml_lib.empty() ? nullptr : f.nvml_lib.c_str()) != GS_OK) {
+    logv(1, "Failed to initialize NVML: %s.", gs_nvml_last_error());
+    logv(1, "If this is a GPU node, did you set the docker default runtime to `nvidia`?");
+    wait_forever();
+  }
+  logv(1, "Fetching devices.");
+  uint32_t count = 0;
+  if (gs_nvml_device_count(&count) != GS_OK || count == 0) {
+    logv(1, "No devices found. Waiting indefinitely.");
+    wait_forever();
+  }
+  logv(1, "Starting FS watcher.");
+  const int ino = inotify_init1(IN_NONBLOCK | IN_CLOEXEC);  // newFSWatcher (watchers.go:10-25)
+  if (ino < 0 || inotify_add_watch(ino, f.socket_dir.c_str(), IN_CREATE | IN_DELETE | IN_MOVED_TO) < 0) {
+    logv(0, "Failed to created FS watcher.");
+    return 1;
+  }
+  logv(1, "Starting OS watcher.");
+  if (pipe(g_sig_pipe) != 0) return 1;
+  struct sigaction sa;
+  memset(&sa, 0, sizeof(sa));
+  sa.sa_handler = on_signal;
+  for (int s : {SIGHUP, SIGINT, SIGTERM, SIGQUIT}) sigaction(s, &sa, nullptr);
+  signal(SIGPIPE, SIG_IGN);
+
+  std::unique_ptr<PluginInstance> inst;
+  bool restart = true;
+  for (;;) {
+    if (restart) {  // gpumanager.go:66-79
+      if (inst) inst->shutdown();
+      inst.reset(new PluginInstance(f, node, unit));
+      std::string err;
+      if (!inst->init(err)) {
+        logv(0, "Failed to get device plugin due to %s", err.c_str());
+        return 1;  // :71-73
+      }
+      if (!inst->serve(err)) {
+        logv(0, "Failed to start device plugin due to %s", err.c_str());
+        return 2;  // :74-76
+      }
+      restart = false;
+    }
+    struct pollfd pf[2] = {{ino, POLLIN, 0}, {g_sig_pipe[0], POLLIN, 0}};
+    const int r = poll(pf, 2, 1000);
+    if (r <= 0) continue;
+    if (pf[0].revents & POLLIN) {  // :82-87
+      alignas(struct inotify_event) char buf[8192];
+      const ssize_t n = read(ino, buf, sizeof(buf));
+      for (ssize_t off = 0; off + (ssize_t)sizeof(struct inotify_event) <= n;) {
+        const struct inotify_event *ev = (const struct inotify_event *)(buf + off);
+        if (ev->len && (ev->mask & IN_CREATE) && strcmp(ev->name, "kubelet.sock") == 0) {
+          logv(1, "inotify: %s created, restarting.", GS_KUBELET_SOCKET);
+          restart = true;
+        }
+        off += (ssize_t)sizeof(struct inotify_event) + ev->len;
+      }
+    }
+    if (pf[1].revents & POLLIN) {
+      unsigned char sigs[64];
+      const ssize_t n = read(g_sig_pipe[0], sigs, sizeof(sigs));
+      for (ssize_t i = 0; i < n; ++i) {
+        if (sigs[i] == SIGHUP) {  // :94-96
+          logv(1, "Received SIGHUP, restarting.");
+          restart = true;
+        } else if (sigs[i] == SIGQUIT) {  // :97-101
+          logv(0, "generate core dump");
+          char name[96];
+          time_t now = time(nullptr);
+          struct tm tmv;
+          localtime_r(&now, &tmv);
+          strftime(name, sizeof(name), "/etc/kubernetes/go_%Y%m%d%H%M%S.txt", &tmv);
+          coredump(name);
+        } else {  // :102-106
+          logv(1, "Received signal \"%d\", shutting down.", (int)sigs[i]);
+          inst->shutdown();
+          close(ino);
+          logv(1, "Shutdown of NVML returned: %d", gs_nvml_close());
+          return 0;
+        }
+      }
+    }
+  }
+}

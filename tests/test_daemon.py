@@ -16,6 +16,12 @@ from gpushare_b200.grpc_harness import KubeletStub
 from oracle import ref_model as R
 from tests.conftest import FAKE_NVML, ROOT
 
+NATIVE_BIN = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "gpushare-device-plugin-v2")
+# the same program twice: daemon.py over either transport, and the native binary (daemon_cpp/)
+PROGRAMS = {"python-native": [sys.executable, "-m", "gpushare_b200.daemon", "--transport", "native"],
+            "python-grpcio": [sys.executable, "-m", "gpushare_b200.daemon", "--transport", "grpcio"],
+            "binary": [NATIVE_BIN]}
+
 
 def test_flag_names_and_defaults_match_reference():
     a = daemon.parse_args([])
@@ -29,8 +35,8 @@ def test_flag_names_and_defaults_match_reference():
     assert a.memory_unit == "MiB" and a.health_check and not a.query_kubelet and a.mps
 
 
-@pytest.mark.parametrize("transport", ["native", "grpcio"])
-def test_daemon_config1_end_to_end(golden_cases, transport):
+@pytest.mark.parametrize("program", sorted(PROGRAMS))
+def test_daemon_config1_end_to_end(golden_cases, program):
     c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
     with tempfile.TemporaryDirectory(prefix="gsd") as d:
         pods = os.path.join(d, "pods.json")
@@ -39,9 +45,9 @@ def test_daemon_config1_end_to_end(golden_cases, transport):
         kubelet.start()
         env = dict(os.environ, NODE_NAME=c["node"], FAKE_NVML_GPUS="8", FAKE_NVML_MEM_MIB="16384",
                    PYTHONPATH=ROOT)
-        proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "-logtostderr", "--v=5",
+        proc = subprocess.Popen(PROGRAMS[program] + ["-logtostderr", "--v=5",
                                  "--memory-unit=GiB", "--nvml-lib", FAKE_NVML, "--socket-dir", d,
-                                 "--pod-source-file", pods, "--health-check", "--transport", transport],
+                                 "--pod-source-file", pods, "--health-check"],
                                 env=env, stderr=subprocess.PIPE, text=True)
         try:
             assert kubelet.wait_registered(30), proc.stderr.read() if proc.poll() is not None else ""
@@ -63,15 +69,17 @@ def test_daemon_config1_end_to_end(golden_cases, transport):
         assert proc.returncode == 0
 
 
-def test_daemon_requires_node_name():
+@pytest.mark.parametrize("program", ["python-native", "binary"])
+def test_daemon_requires_node_name(program):
     env = {k: v for k, v in os.environ.items() if k != "NODE_NAME"}
     env["PYTHONPATH"] = ROOT
-    out = subprocess.run([sys.executable, "-m", "gpushare_b200.daemon", "--nvml-lib", FAKE_NVML],
+    out = subprocess.run(PROGRAMS[program] + ["--nvml-lib", FAKE_NVML],
                          env=env, capture_output=True, text=True, timeout=60)
     assert out.returncode != 0 and "Please set env NODE_NAME" in out.stderr
 
 
-def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases):
+@pytest.mark.parametrize("program", ["python-native", "binary"])
+def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, program):
     """gpumanager.go:83-96: kubelet.sock re-created => tear down, re-enumerate, register again;
     SIGHUP => the same."""
     c = next(x for x in golden_cases if x["name"] == "G1-binpack-1")
@@ -82,7 +90,7 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases):
         kubelet.start()
         env = dict(os.environ, NODE_NAME=c["node"], FAKE_NVML_GPUS="2", FAKE_NVML_MEM_MIB="4096",
                    PYTHONPATH=ROOT)
-        proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "--v=1", "--nvml-lib", FAKE_NVML,
+        proc = subprocess.Popen(PROGRAMS[program] + ["--v=1", "--nvml-lib", FAKE_NVML,
                                  "--socket-dir", d, "--pod-source-file", pods],
                                 env=env, stderr=subprocess.PIPE, text=True)
         try:
