@@ -20,7 +20,10 @@
 #include <sys/stat.h>
 
 #include <atomic>
+#include <condition_variable>
+#include <deque>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <unordered_map>
@@ -90,6 +93,7 @@ struct Stream {
 };
 
 struct Conn {
+  uint64_t serial = 0;  // names the connection for answers that come back from the worker
   Wire w;
   Decoder hpack;
   bool preface_seen = false;
@@ -105,6 +109,23 @@ struct Conn {
   uint32_t cont_stream = 0;  // stream whose header block awaits CONTINUATION frames
   uint8_t cont_flags = 0;    // flags of the HEADERS frame that opened it
   std::vector<Header> headers;
+};
+
+// An Allocate handed to the caller's callback (gs_server_config.allocate). The callback may
+// spend seconds on the network (lister ladders, PATCH), so it runs on a worker thread: the
+// serving thread keeps answering ListAndWatch and other connections meanwhile. One worker,
+// so callbacks stay serialised exactly as m.Lock() serialises Allocate (allocate.go:60).
+struct AllocJob {
+  uint64_t conn_serial;
+  uint32_t stream;
+  std::unique_ptr<Buf> req;  // gRPC-framed request: 5-byte prefix + AllocateRequest
+};
+struct AllocDone {
+  uint64_t conn_serial;
+  uint32_t stream;
+  int rc;
+  std::vector<uint8_t> resp;
+  std::unique_ptr<Buf> req;  // handed back for reuse
 };
 
 }  // namespace
@@ -135,6 +156,16 @@ struct gs_server {
   std::vector<uint8_t> ok_trailers;    // grpc-status 0
   std::vector<uint8_t> resp;           // Allocate response scratch
   std::vector<struct iovec> iov_scratch;
+  uint64_t next_conn_serial = 1;
+
+  std::thread worker;
+  std::mutex job_mu;
+  std::condition_variable job_cv;
+  std::deque<AllocJob> jobs;
+  std::deque<AllocDone> done;
+  bool worker_stop = false;
+  void worker_main();
+  void deliver_done();
 
   // stats (read from other threads)
   std::atomic<uint64_t> n_connections{0}, n_requests{0}, n_allocate{0}, n_law_messages{0},
@@ -490,16 +521,21 @@ bool gs_server::on_request_complete(Conn &c, Stream &s) {
       return send_error(c, s, kUnimplemented, "implement me");
     case kAllocate: {
       n_allocate.fetch_add(1, std::memory_order_relaxed);
+      if (allocate_fn) {  // answered by deliver_done once the callback returns
+        AllocJob j{c.serial, s.id, std::move(s.req)};
+        {
+          std::lock_guard<std::mutex> lk(job_mu);
+          jobs.push_back(std::move(j));
+        }
+        job_cv.notify_one();
+        return true;
+      }
       int rc = GS_OK;
       for (int attempt = 0; attempt < 4; ++attempt) {
-        if (allocate_fn) {
-          rc = allocate_fn(user, msg, mlen, resp.data(), resp.size(), &out_len);
-        } else {
-          gs_alloc_result res;
-          rc = gs_plugin_allocate(plugin, msg, mlen, resp.data(), resp.size(), &res);
-          out_len = res.resp_len;
-          if (rc == GS_OK && decision_fn) decision_fn(user, &res);
-        }
+        gs_alloc_result res;
+        rc = gs_plugin_allocate(plugin, msg, mlen, resp.data(), resp.size(), &res);
+        out_len = res.resp_len;
+        if (rc == GS_OK && decision_fn) decision_fn(user, &res);
         if (rc != GS_E_NOSPACE) break;
         resp.resize(out_len > resp.size() * 2 ? out_len : resp.size() * 2);
       }
@@ -713,6 +749,72 @@ bool gs_server::handle_frame(Conn &c, const FrameHeader &h) {
   }
 }
 
+// ---- the Allocate callback worker --------------------------------------------------------------
+
+void gs_server::worker_main() {
+  std::vector<uint8_t> out(64 << 10);
+  for (;;) {
+    AllocJob j;
+    {
+      std::unique_lock<std::mutex> lk(job_mu);
+      job_cv.wait(lk, [&] { return worker_stop || !jobs.empty(); });
+      if (jobs.empty()) return;  // stop requested and nothing left
+      j = std::move(jobs.front());
+      jobs.pop_front();
+    }
+    const uint8_t *msg = j.req->p + 5;
+    const size_t mlen = j.req->n - 5;
+    size_t out_len = 0;
+    int rc = GS_OK;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+      rc = allocate_fn(user, msg, mlen, out.data(), out.size(), &out_len);
+      if (rc != GS_E_NOSPACE) break;
+      out.resize(out_len > out.size() * 2 ? out_len : out.size() * 2);
+    }
+    AllocDone d{j.conn_serial, j.stream, rc, {}, std::move(j.req)};
+    if (rc == GS_OK) d.resp.assign(out.begin(), out.begin() + (long)out_len);
+    {
+      std::lock_guard<std::mutex> lk(job_mu);
+      done.push_back(std::move(d));
+    }
+    const uint64_t one = 1;
+    if (write(wake_fd, &one, sizeof(one)) < 0) {
+    }
+  }
+}
+
+// Serving thread: send the answers the worker finished. A connection or stream that went
+// away meanwhile (kubelet gave up, RST_STREAM) simply has nobody to answer.
+void gs_server::deliver_done() {
+  std::deque<AllocDone> ready;
+  {
+    std::lock_guard<std::mutex> lk(job_mu);
+    ready.swap(done);
+  }
+  for (AllocDone &d : ready) {
+    for (auto &cp : conns) {
+      Conn &c = *cp;
+      if (c.serial != d.conn_serial || c.dead) continue;
+      auto it = c.streams.find(d.stream);
+      if (it == c.streams.end()) break;
+      Stream &s = it->second;
+      if (d.req) {
+        d.req->n = 0;
+        s.req = std::move(d.req);  // close_stream returns it to the pool
+      }
+      bool ok;
+      if (d.rc == GS_E_WIRE)  // what grpc-go answers when proto.Unmarshal of the request fails
+        ok = send_error(c, s, kInternal, "grpc: error unmarshalling request: malformed AllocateRequest");
+      else if (d.rc != GS_OK)
+        ok = send_error(c, s, kUnknownCode, std::string("Allocate: ") + gs_strerror(d.rc));
+      else
+        ok = send_unary(c, s, d.resp.data(), d.resp.size());
+      if (!ok) c.dead = true;
+      break;
+    }
+  }
+}
+
 // ---- the serving thread --------------------------------------------------------------------
 
 void gs_server::drop_conn(Conn &c) {
@@ -736,6 +838,7 @@ void gs_server::accept_one() {
   set_big_buffers(fd, 4 << 20);
   std::unique_ptr<Conn> c(new Conn());
   c->w.fd = fd;
+  c->serial = next_conn_serial++;
   // server connection preface (RFC 7540 3.5): SETTINGS, then open the connection window
   const uint16_t ids[3] = {kSetMaxConcurrentStreams, kSetInitialWindowSize, kSetMaxFrameSize};
   const uint32_t vals[3] = {(uint32_t)kMaxStreams, kOurStreamWindow, kOurMaxFrame};
@@ -785,6 +888,7 @@ void gs_server::run() {
       uint64_t v;
       while (read(wake_fd, &v, sizeof(v)) > 0) {
       }
+      deliver_done();
     }
     for (size_t i = 0; i < n_conns; ++i) {
       if (pfds[2 + i].revents & (POLLIN | POLLHUP | POLLERR)) serve_conn(*conns[i]);
@@ -851,6 +955,7 @@ int gs_server_start(gs_plugin *plugin, const gs_server_config *cfg, gs_server **
   }
   gs_internal::plugin_add_wake_fd(plugin, s->wake_fd);
   gs_server *raw = s.get();
+  if (s->allocate_fn) s->worker = std::thread([raw] { raw->worker_main(); });
   s->thread = std::thread([raw] { raw->run(); });
 
   // server.go:131: dial our own socket (blocking, 5 s) to know that the server answers
@@ -874,6 +979,13 @@ int gs_server_stop(gs_server *s) {
   if (write(s->wake_fd, &one, sizeof(one)) < 0) {
   }
   if (s->thread.joinable()) s->thread.join();
+  {
+    std::lock_guard<std::mutex> lk(s->job_mu);
+    s->worker_stop = true;
+    s->jobs.clear();  // their streams are gone with the connections
+  }
+  s->job_cv.notify_all();
+  if (s->worker.joinable()) s->worker.join();
   gs_internal::plugin_remove_wake_fd(s->plugin, s->wake_fd);
   close(s->wake_fd);
   close(s->listen_fd);

@@ -221,8 +221,11 @@ class PluginInstance:
                             g, nbytes, pod_index))
                 except L.GpushareError as e:
                     log(self.a.v, 1, "probe skipped: %s" % e)
-            for s in self.probes.values():
+            for g2, s in self.probes.items():
                 s.pump()
+                # the range belongs to the tenant: give it back the moment the sweep is over
+                if s.inflight is None and not s.pending and g2 in self.arenas:
+                    s.probe.free(self.arenas.pop(g2))
             if self.a.health_probe_interval and time.time() - last_sweep >= self.a.health_probe_interval:
                 last_sweep = time.time()
                 self.health_sweep()

@@ -146,7 +146,7 @@ struct ProbeWorker {
     gs_law_mark_unhealthy_gpu(table, gpu);
     gs_plugin_notify_health(plugin);
   }
-  void harvest(int gpu, bool block) {
+  void harvest(int gpu, bool block, const char *label = "probe") {
     if (!inflight[gpu]) return;
     gs_probe *p = probes[gpu];
     if (!block && gs_probe_poll(p) != GS_OK) return;
@@ -154,12 +154,17 @@ struct ProbeWorker {
     gs_probe_timing tm;
     if (gs_probe_wait(p, &r, 1, &tm) == GS_OK) {
       const double ms = tm.write_ms + tm.verify_ms + tm.scrub_ms;
-      logv(1, "probe: gpu %d swept %llu bytes at %.0f GB/s, %llu mismatching words", gpu,
+      logv(1, "%s: gpu %d swept %llu bytes at %.0f GB/s, %llu mismatching words", label, gpu,
            (unsigned long long)tm.bytes, ms > 0 ? 2.0 * (double)tm.bytes / ms / 1e6 : 0.0,
            (unsigned long long)r.mismatches);
       if (r.mismatches) mark_bad(gpu);
     }
     inflight[gpu] = false;
+    // the range belongs to the tenant: give it back the moment the sweep is over
+    if (arenas.count(gpu)) {
+      gs_probe_mem_free(p, arenas[gpu]);
+      arenas.erase(gpu);
+    }
   }
   void start(const ProbeJob &j) {
     gs_probe *p = probes[j.gpu];
@@ -203,11 +208,7 @@ struct ProbeWorker {
       if (gs_probe_mem_info(kv.second, &free_b, &total_b) != GS_OK || free_b < (3ull << 30)) continue;
       ProbeJob j{kv.first, free_b - (2ull << 30), 0x5eed};
       start(j);
-      harvest(kv.first, true);
-      if (arenas.count(kv.first)) {
-        gs_probe_mem_free(kv.second, arenas[kv.first]);
-        arenas.erase(kv.first);
-      }
+      harvest(kv.first, true, "health probe");
     }
   }
   void run() {

@@ -310,9 +310,12 @@ GS_API int gs_plugin_stopped(const gs_plugin *p);
  * answers without a registered decompressor).                                  */
 typedef struct gs_server gs_server;
 /* Optional replacement for the Allocate body, for callers whose pod source is
- * the network (podmanager.go:187-245, allocate.go:136): called on the serving
- * thread with the AllocateRequest bytes; writes the AllocateResponse bytes.
- * GS_E_NOSPACE with *resp_len = required size asks for a larger buffer.        */
+ * the network (podmanager.go:187-245, allocate.go:136): called with the
+ * AllocateRequest bytes; writes the AllocateResponse bytes. Calls are made one
+ * at a time, in arrival order, on a worker thread of the server (the callback
+ * may block on the network for seconds; ListAndWatch and other connections
+ * keep being served meanwhile). GS_E_NOSPACE with *resp_len = required size
+ * asks for a larger buffer (the callback is then called again: keep the answer). */
 typedef int (*gs_server_allocate_fn)(void *user, const uint8_t *req, size_t req_len,
                                      uint8_t *resp, size_t resp_cap, size_t *resp_len);
 /* Optional hook after each decision of the built-in Allocate (e.g. queue a

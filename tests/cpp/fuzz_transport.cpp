@@ -309,7 +309,17 @@ static int run_fuzz(int iterations) {
   return 0;
 }
 
-static int run_race(int seconds) {
+// the caller-supplied Allocate (gs_server_config.allocate): runs on the server's worker thread
+static int allocate_via_callback(void *user, const uint8_t *req, size_t req_len, uint8_t *resp, size_t cap,
+                                 size_t *resp_len) {
+  gs_alloc_result res;
+  const int rc = gs_plugin_allocate((gs_plugin *)user, req, req_len, resp, cap, &res);
+  *resp_len = res.resp_len;
+  usleep(200);  // a little "network"
+  return rc;
+}
+
+static int run_race(int seconds, bool with_callback) {
   const char *uuid = "GPU-0f9b9cf4-2b1c-4a3e-9c1d-5e2f6a7b8c9d";
   gs_table *t = make_table(uuid);
   gs_plugin *p = nullptr;
@@ -318,6 +328,10 @@ static int run_race(int seconds) {
   gs_server_config cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.socket_path = sock.c_str();
+  if (with_callback) {
+    cfg.allocate = allocate_via_callback;
+    cfg.user = p;
+  }
   gs_server *srv = nullptr;
   CHECK(gs_server_start(p, &cfg, &srv) == GS_OK);
   const std::vector<uint8_t> req = allocate_request(uuid, 8);
@@ -373,7 +387,8 @@ static int run_race(int seconds) {
   th[3].join();
   CHECK(gs_server_stop(srv) == GS_OK);  // ends the watch stream with OK
   th[2].join();
-  printf("race: %ld allocate calls, %ld lists\n", calls.load(), lists.load());
+  printf("race%s: %ld allocate calls, %ld lists\n", with_callback ? " (callback worker)" : "", calls.load(),
+         lists.load());
   CHECK(calls.load() > 10 && lists.load() > 2);
   gs_plugin_free(p);
   gs_table_free(t);
@@ -387,7 +402,7 @@ int main(int argc, char **argv) {
   const std::string mode = argc > 1 ? argv[1] : "fuzz";
   const int n = argc > 2 ? atoi(argv[2]) : 0;
   int rc;
-  if (mode == "race") rc = run_race(n > 0 ? n : 2);
+  if (mode == "race") rc = run_race(n > 0 ? n : 2, false) || run_race(n > 0 ? n : 2, true);
   else rc = run_fuzz(n > 0 ? n : 1500);
   rmdir(tmpl);
   if (rc == 0) printf("TRANSPORT %s OK\n", mode == "race" ? "RACE" : "FUZZ");

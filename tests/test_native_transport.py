@@ -245,6 +245,54 @@ def test_python_allocate_behind_native_server(golden_cases, sockdir):
         srv.Stop()
 
 
+def test_slow_python_allocate_does_not_hold_up_the_watch_stream(golden_cases, sockdir):
+    """An Allocate callback that sits on the network (lister ladders) runs on the server's
+    worker: health re-advertisements and other RPCs go out meanwhile; Allocates stay in order."""
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    inner = plug.Allocate
+    order = []
+
+    def slow(request):
+        order.append(len(request))
+        time.sleep(0.8)
+        return inner(request)
+    plug.Allocate = slow
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    try:
+        watcher = NativeClient(srv.socket)
+        sid = watcher.open_stream("ListAndWatch")
+        watcher.next_message(sid)
+        results = {}
+
+        def caller(name, req):
+            with NativeClient(srv.socket) as cl:
+                results[name] = R.decode_allocate_response(cl.call("Allocate", req))
+        r1 = R.encode_allocate_request(c["steps"][0]["request"])
+        r2 = R.encode_allocate_request(c["steps"][1]["request"]) + b""
+        t1 = threading.Thread(target=caller, args=("first", r1))
+        t1.start()
+        time.sleep(0.15)
+        t2 = threading.Thread(target=caller, args=("second", r2))
+        t2.start()
+        time.sleep(0.1)
+        t0 = time.time()
+        plug.unhealthy(0)
+        msg = watcher.next_message(sid, timeout_ms=3000)
+        assert time.time() - t0 < 0.4 and msg.count(b"Unhealthy") == 16     # not behind the callback
+        assert watcher.call("GetDevicePluginOptions") == b""
+        assert time.time() - t0 < 0.5
+        t1.join(10)
+        t2.join(10)
+        assert results["first"] == c["steps"][0]["expect_envs"]
+        assert results["second"] == c["steps"][1]["expect_envs"]
+        assert len(order) == 2
+        watcher.close()
+    finally:
+        srv.Stop()
+
+
 def test_many_calls_and_two_clients(golden_cases, sockdir):
     """Several hundred calls on one connection (HPACK dynamic table churn on the grpc-core
     side), two connections at once, and a client that vanishes mid-stream."""

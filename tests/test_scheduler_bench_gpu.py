@@ -56,6 +56,7 @@ def test_bench_line_contract():
     assert r["value"] > 1000 and r["e2e"]["value"] > 500 and r["gpu_launches"] >= 2
     assert r["roofline"]["bound"] == "hbm" and r["roofline"]["achieved"] > 3000
     assert r["probe"]["bad_slices"] == 0 and "workload" in r["config"]
+    assert r["over_socket"]["value"] > 500 and r["over_socket"]["allocate_calls_served_rank0"] >= 2 * 256
 
 
 def test_colocation_tool_small_scale():
@@ -69,7 +70,8 @@ def test_colocation_tool_small_scale():
     assert len(r["probe"]["per_gpu"]) >= 1 and r["allocate"]["decisions"] == len(r["tenants_gib"])
 
 
-def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
+@pytest.mark.parametrize("program", ["python", "binary"])
+def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path, program):
     """The daemon against the real NVML and GPU: enumerate, serve, Allocate for a pod bound to
     GPU 0, sweep the granted range, and sweep free memory on the health timer."""
     import signal
@@ -88,7 +90,9 @@ def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
             {"resources": {"limits": {"aliyun.com/gpu-mem": "2"}}}]}, "status": {"phase": "Pending"}}]}
     (tmp_path / "pods.json").write_text(json.dumps(pods))
     env = dict(os.environ, NODE_NAME="node-a", PYTHONPATH=ROOT)
-    proc = subprocess.Popen([sys.executable, "-m", "gpushare_b200.daemon", "--v=1", "--memory-unit=GiB",
+    exe = [sys.executable, "-m", "gpushare_b200.daemon"] if program == "python" else [
+        os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "gpushare-device-plugin-v2")]
+    proc = subprocess.Popen(exe + ["--v=1", "--memory-unit=GiB",
                              "--socket-dir", str(tmp_path), "--pod-source-file", str(tmp_path / "pods.json"),
                              "--no-register", "--probe", "--health-check", "--health-probe-interval=1"],
                             env=env, stderr=subprocess.PIPE, text=True)
