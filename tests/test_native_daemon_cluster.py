@@ -269,3 +269,76 @@ def test_binary_links_only_what_it_should():
     out = subprocess.run(["ldd", NATIVE_BIN], capture_output=True, text=True).stdout
     assert "libgpushare_core.so" in out and "libssl" in out and "oracle" not in out
     assert ROOT in out or "not found" not in out
+
+
+def test_pod_decoding_matches_the_python_host(tmp_path):
+    """daemon_cpp/json.h + pod_from_json against api.Pod.from_k8s on generated PodLists:
+    escapes, non-ASCII, surrogate pairs, missing and null fields, quantities in every
+    accepted form, numbers where strings are usual, wrapping sums."""
+    import random
+
+    from gpushare_b200 import _lib as L
+    from gpushare_b200 import api
+    exe = str(tmp_path / "pods_from_json")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined",
+                    "-I" + os.path.join(ROOT, "include"),
+                    "-I" + os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "daemon_cpp"),
+                    os.path.join(ROOT, "tests", "cpp", "pods_from_json.cpp"),
+                    os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc", "gosem.cpp"),
+                    os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc", "errors.cpp"),
+                    "-o", exe, "-lssl", "-lcrypto"], check=True)
+    rng = random.Random(20261106)
+    words = ["a", "binpack-1", "kube-system", "node-a", "p\"q", "back\\slash", "tab\there", "nl\nx", "été",
+             "中文", "\U0001f600", "", "x" * 300, "ctl\x01"]
+    quantities = ["2", "1024", "1Ki", "1500m", "2Gi", "1e3", "0", "+3", ".5", "12E2", "18446744073709551615",
+                  "9223372036854775807", 7, 40, 0]
+
+    def pod():
+        p = {"metadata": {}, "spec": {}, "status": {"phase": rng.choice(["Pending", "Running"])}}
+        for k in ("uid", "namespace", "name"):
+            if rng.random() < 0.9:
+                p["metadata"][k] = rng.choice(words)
+        if rng.random() < 0.8:
+            ann = {}
+            for k in ("ALIYUN_COM_GPU_MEM_IDX", "ALIYUN_COM_GPU_MEM_ASSUME_TIME", "ALIYUN_COM_GPU_MEM_ASSIGNED", "other"):
+                if rng.random() < 0.7:
+                    ann[k] = rng.choice(words + ["0", "-1", "true", "false", "1700000000000000000"])
+            p["metadata"]["annotations"] = ann if rng.random() < 0.9 else None
+        if rng.random() < 0.9:
+            p["spec"]["nodeName"] = rng.choice(words)
+        cs = []
+        for _ in range(rng.randrange(4)):
+            c = {"name": rng.choice(words)}
+            r = rng.random()
+            if r < 0.6:
+                c["resources"] = {"limits": {"aliyun.com/gpu-mem": rng.choice(quantities), "cpu": "1"}}
+            elif r < 0.7:
+                c["resources"] = {"limits": {"cpu": "500m"}}
+            elif r < 0.8:
+                c["resources"] = {}
+            cs.append(c)
+        if rng.random() < 0.95:
+            p["spec"]["containers"] = cs
+        if rng.random() < 0.05:
+            del p["spec"]
+        return p
+
+    for trial in range(40):
+        items = [pod() for _ in range(rng.randrange(1, 12))]
+        text = json.dumps({"items": items}, ensure_ascii=rng.random() < 0.5)
+        out = subprocess.run([exe], input=text.encode(), capture_output=True, timeout=60)
+        assert out.returncode == 0, out.stderr.decode()[-2000:]
+        lines = out.stdout.decode().splitlines()
+        assert len(lines) == len(items)
+        for line, p in zip(lines, items):
+            try:
+                want = api.Pod.from_k8s(p)
+            except L.GpushareError:
+                assert line == "POD-ERROR"
+                continue
+            got = json.loads(line)
+            assert got == [want.uid, want.namespace, want.name, want.node_name, want.gpu_mem_limit,
+                           want.ann_idx, want.ann_assume_time, want.ann_assigned], (trial, p)
+    for bad in (b"", b"{", b'{"items": [}', b'{"a": "\\x"}', b'[1,]', b'{"items": [{"metadata": "\\ud800"}]}'):
+        out = subprocess.run([exe], input=bad, capture_output=True, timeout=60)
+        assert out.returncode == 0 and (out.stdout in (b"PARSE-ERROR\n", b"") or b"[" in out.stdout)
