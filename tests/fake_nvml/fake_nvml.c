@@ -8,8 +8,10 @@
  *   FAKE_NVML_MEM_MIB   total memory per GPU in MiB (default 16384)
  *   FAKE_NVML_NO_EVENTS comma list of GPU indices that answer NOT_SUPPORTED to
  *                       nvmlDeviceRegisterEvents
+ *   FAKE_NVML_EVENT_FIFO path of a FIFO read for lines "<gpu_index_or_-1> <xid>": events for
+ *                       a daemon running in another process
  * Events are injected with fake_nvml_push_event(gpu_index_or_-1, xid), an extra
- * export the tests call through ctypes.
+ * export the tests call through ctypes, or through the FIFO above.
  * UUIDs follow SURVEY 8(d): GPU-%08x-0000-0000-0000-%012x from the index.
  */
 #include <pthread.h>
@@ -52,8 +54,34 @@ static int g_qh = 0, g_qt = 0;
 
 #define EXPORT __attribute__((visibility("default")))
 
+EXPORT void fake_nvml_push_event(int gpu, unsigned long long xid);
+
+static char g_fifo[512];
+static int g_fifo_started = 0;
+static void *fifo_reader(void *arg) {
+  (void)arg;
+  for (;;) {
+    FILE *f = fopen(g_fifo, "r"); /* blocks until a writer opens the FIFO */
+    if (!f) return NULL;
+    char line[128];
+    while (fgets(line, sizeof line, f)) {
+      int gpu;
+      unsigned long long xid;
+      if (sscanf(line, "%d %llu", &gpu, &xid) == 2) fake_nvml_push_event(gpu, xid);
+    }
+    fclose(f); /* writer went away: wait for the next one */
+  }
+}
+
 EXPORT nvmlReturn_t nvmlInit_v2(void) {
-  const char *s = getenv("FAKE_NVML_GPUS");
+  const char *s = getenv("FAKE_NVML_EVENT_FIFO");
+  if (s && *s && !g_fifo_started) {
+    pthread_t t;
+    snprintf(g_fifo, sizeof g_fifo, "%s", s);
+    g_fifo_started = 1;
+    if (pthread_create(&t, NULL, fifo_reader, NULL) == 0) pthread_detach(t);
+  }
+  s = getenv("FAKE_NVML_GPUS");
   g_n = s ? atoi(s) : 8;
   if (g_n < 0) g_n = 0;
   if (g_n > MAX_GPUS) g_n = MAX_GPUS;

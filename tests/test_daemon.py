@@ -122,3 +122,53 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, prog
         assert proc.returncode == 0
         err = proc.stderr.read()
         assert "kubelet.sock created, restarting." in err and "Received SIGHUP, restarting." in err
+
+
+@pytest.mark.parametrize("program", ["python-native", "binary"])
+def test_daemon_health_events_reach_the_watch_stream(program):
+    """BASELINE config 5 through a whole daemon: XID 79 on GPU 3 re-advertises that GPU's 16
+    devices as Unhealthy, XID 31 is ignored (nvidia.go:134), an event without a device takes
+    every GPU down (nvidia.go:138-143); Allocate keeps answering throughout."""
+    from gpushare_b200.native_transport import NativeClient
+    with tempfile.TemporaryDirectory(prefix="gsd") as d:
+        pods = os.path.join(d, "pods.json")
+        json.dump({"items": []}, open(pods, "w"))
+        fifo = os.path.join(d, "xid.fifo")
+        os.mkfifo(fifo)
+        env = dict(os.environ, NODE_NAME="node-a", FAKE_NVML_GPUS="8", FAKE_NVML_MEM_MIB="16384",
+                   FAKE_NVML_EVENT_FIFO=fifo, PYTHONPATH=ROOT)
+        proc = subprocess.Popen(PROGRAMS[program] + ["--v=1", "--nvml-lib", FAKE_NVML, "--socket-dir", d,
+                                                      "--pod-source-file", pods, "--health-check", "--no-register"],
+                                env=env, stderr=subprocess.PIPE, text=True)
+        try:
+            sock = os.path.join(d, "aliyungpushare.sock")
+            deadline = time.time() + 30
+            while not os.path.exists(sock) and time.time() < deadline:
+                time.sleep(0.05)
+            with NativeClient(sock, timeout_ms=10000) as cl, open(fifo, "w") as events:
+                sid = cl.open_stream("ListAndWatch")
+                first = R.decode_list_and_watch(cl.next_message(sid))
+                assert len(first) == 128 and all(h == "Healthy" for _, h in first)
+                time.sleep(0.3)                         # the health thread is up by now
+                events.write("3 79\n")
+                events.flush()
+                t0 = time.time()
+                second = R.decode_list_and_watch(cl.next_message(sid, timeout_ms=5000))
+                assert time.time() - t0 < 2.5
+                assert [i for i, h in second if h == "Unhealthy"] == [i for i, _ in first[48:64]]
+                events.write("1 31\n")                 # an application error: not the GPU's fault
+                events.flush()
+                with pytest.raises(TimeoutError):
+                    cl.next_message(sid, timeout_ms=1500)
+                assert b"no-gpu-has-1GiB-to-run" in cl.call("Allocate", R.encode_allocate_request([["x"]]))
+                events.write("-1 48\n")
+                events.flush()
+                third = R.decode_list_and_watch(cl.next_message(sid, timeout_ms=5000))
+                assert all(h == "Unhealthy" for _, h in third)
+        finally:
+            proc.send_signal(signal.SIGTERM)
+            try:
+                proc.wait(10)
+            except subprocess.TimeoutExpired:
+                proc.kill()
+        assert proc.returncode == 0, proc.stderr.read()[-2000:]
