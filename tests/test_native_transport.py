@@ -438,3 +438,81 @@ def test_transport_under_thread_sanitizer(tmp_path):
     out = subprocess.run([exe, "race", "2"], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "TRANSPORT RACE OK" in out.stdout \
         and "WARNING: ThreadSanitizer" not in out.stderr, (out.stdout + out.stderr)[-4000:]
+
+
+def _frame(ftype, flags, stream, payload=b""):
+    return len(payload).to_bytes(3, "big") + bytes([ftype, flags]) + stream.to_bytes(4, "big") + payload
+
+
+def _lit(name, value):                                   # HPACK literal without indexing, new name
+    return b"\x00" + bytes([len(name)]) + name + bytes([len(value)]) + value
+
+
+def _read_frames(sock):
+    buf = b""
+    while True:
+        chunk = sock.recv(65536)
+        if not chunk:
+            break
+        buf += chunk
+    frames, i = [], 0
+    while i + 9 <= len(buf):
+        n = int.from_bytes(buf[i:i + 3], "big")
+        frames.append((buf[i + 3], buf[i + 4], int.from_bytes(buf[i + 5:i + 9], "big"), buf[i + 9:i + 9 + n]))
+        i += 9 + n
+    return frames
+
+
+def test_frames_grpc_core_never_sends(golden_cases, sockdir):
+    """CONTINUATION, padded and prioritised HEADERS, padded DATA split over several frames, a
+    PRIORITY frame, an unknown frame type, a PING: RFC 7540 says all of it is legal, and the
+    call must be answered like any other."""
+    import socket as pysock
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    try:
+        req = R.encode_allocate_request(c["steps"][0]["request"])
+        body = b"\x00" + len(req).to_bytes(4, "big") + req
+        block = (b"\x83\x86" + b"\x04" + bytes([len(b"/v1beta1.DevicePlugin/Allocate")]) + b"/v1beta1.DevicePlugin/Allocate"
+                 + _lit(b"content-type", b"application/grpc") + _lit(b"te", b"trailers")
+                 + _lit(b"x-filler", b"f" * 100))
+        pad = b"\x00" * 7
+        headers_payload = bytes([len(pad)]) + b"\x80\x00\x00\x00\x10" + block[:20] + pad    # PADDED | PRIORITY
+        session = (b"PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n" + _frame(4, 0, 0)
+                   + _frame(2, 0, 1, b"\x00\x00\x00\x00\x05")                               # PRIORITY
+                   + _frame(0x42, 0xff, 0, b"extension")                                    # unknown type
+                   + _frame(6, 0, 0, b"pingpong")
+                   + _frame(1, 0x08 | 0x20, 1, headers_payload)                             # no END_HEADERS
+                   + _frame(9, 0, 1, block[20:60]) + _frame(9, 0x04, 1, block[60:])         # CONTINUATION x2
+                   + _frame(0, 0x08, 1, b"\x03" + body[:10] + b"\x00" * 3)                  # padded DATA
+                   + _frame(0, 0, 1, b"")                                                   # empty DATA
+                   + _frame(0, 0x01, 1, body[10:]))                                         # END_STREAM
+        s = pysock.socket(pysock.AF_UNIX, pysock.SOCK_STREAM)
+        s.settimeout(5)
+        s.connect(srv.socket)
+        s.sendall(session)
+        s.shutdown(pysock.SHUT_WR)
+        frames = _read_frames(s)
+        s.close()
+        assert (6, 1, 0, b"pingpong") in frames                                             # PING ack
+        data = b"".join(p for t, f, sid, p in frames if t == 0 and sid == 1)
+        assert data[0] == 0 and int.from_bytes(data[1:5], "big") == len(data) - 5
+        assert R.decode_allocate_response(data[5:]) == c["steps"][0]["expect_envs"]
+        trailers = [p for t, f, sid, p in frames if t == 1 and sid == 1 and f & 0x01]
+        assert len(trailers) == 1 and trailers[0].endswith(b"\x0bgrpc-status\x010")
+        assert not any(t == 7 and int.from_bytes(p[4:8], "big") != 0 for t, f, sid, p in frames)   # no error GOAWAY
+        # CONTINUATION interrupted by another frame is a connection error (RFC 7540 6.10)
+        s = pysock.socket(pysock.AF_UNIX, pysock.SOCK_STREAM)
+        s.settimeout(5)
+        s.connect(srv.socket)
+        s.sendall(b"PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n" + _frame(4, 0, 0) + _frame(1, 0, 1, block[:20])
+                  + _frame(6, 0, 0, b"12345678"))
+        s.shutdown(pysock.SHUT_WR)
+        frames = _read_frames(s)
+        s.close()
+        goaway = [p for t, f, sid, p in frames if t == 7]
+        assert goaway and int.from_bytes(goaway[0][4:8], "big") == 1                        # PROTOCOL_ERROR
+    finally:
+        srv.Stop()
