@@ -21,6 +21,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "gpushare.h"
@@ -214,17 +215,38 @@ int gs_table_build(const char *const *uuids, const uint32_t *uuid_lens, uint32_t
   t->current_seg.resize(n_gpus);
   t->current_gen.assign(n_gpus, 0);
   t->current_valid.assign(n_gpus, 0);
-  for (uint32_t g = 0; g < n_gpus; ++g) {
-    t->bad_count[g].store(0, std::memory_order_relaxed);
-    t->gpu_gen[g].store(0, std::memory_order_relaxed);
-    const size_t sz = uniform_segment_size(t->uuids[g].size(), units_per_gpu, true);
-    t->healthy_size[g] = sz;
-    t->unhealthy_size[g] = uniform_segment_size(t->uuids[g].size(), units_per_gpu, false);
-    t->healthy_seg[g].resize(sz);
-    uint8_t *end = encode_range(t->healthy_seg[g].data(), t->uuids[g], 0, units_per_gpu, true,
-                                nullptr);
-    if ((size_t)(end - t->healthy_seg[g].data()) != sz) return GS_E_INVAL;  // size model broken
+  std::atomic<bool> broken{false};
+  gs_table *tp = t.get();
+  auto build_gpu = [tp, units_per_gpu, &broken](uint32_t g) {
+    tp->bad_count[g].store(0, std::memory_order_relaxed);
+    tp->gpu_gen[g].store(0, std::memory_order_relaxed);
+    const size_t sz = uniform_segment_size(tp->uuids[g].size(), units_per_gpu, true);
+    tp->healthy_size[g] = sz;
+    tp->unhealthy_size[g] = uniform_segment_size(tp->uuids[g].size(), units_per_gpu, false);
+    tp->healthy_seg[g].resize(sz);
+    uint8_t *end = encode_range(tp->healthy_seg[g].data(), tp->uuids[g], 0, units_per_gpu, true, nullptr);
+    if ((size_t)(end - tp->healthy_seg[g].data()) != sz) broken.store(true);  // size model broken
+  };
+  // The segments are independent: above ~64 k devices (one B200 at MiB is 183 359) encode them
+  // on one thread per GPU, up to eight. This is the restart path (kubelet.sock re-created).
+  uint32_t workers = 1;
+  if (n_gpus > 1 && units_per_gpu * n_gpus >= 65536) {
+    workers = std::thread::hardware_concurrency();
+    if (workers > 8) workers = 8;
+    if (workers > n_gpus) workers = n_gpus;
+    if (workers < 1) workers = 1;
   }
+  if (workers <= 1) {
+    for (uint32_t g = 0; g < n_gpus; ++g) build_gpu(g);
+  } else {
+    std::vector<std::thread> pool;
+    for (uint32_t k = 0; k < workers; ++k)
+      pool.emplace_back([k, workers, n_gpus, &build_gpu] {
+        for (uint32_t g = k; g < n_gpus; g += workers) build_gpu(g);
+      });
+    for (auto &th : pool) th.join();
+  }
+  if (broken.load()) return GS_E_INVAL;
   *out = t.release();
   return GS_OK;
 }
