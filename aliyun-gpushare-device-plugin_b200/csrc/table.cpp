@@ -469,25 +469,40 @@ int gs_law_payload(gs_table *t, gs_iovec *iov, uint32_t cap, uint32_t *n) {
   *n = t->n_gpus;
   if (!iov || cap < t->n_gpus) return GS_E_NOSPACE;
   std::lock_guard<std::mutex> lk(t->seg_mu);
+  std::vector<uint32_t> stale;  // GPUs whose cached segment predates their last health change
   for (uint32_t g = 0; g < t->n_gpus; ++g) {
-    const uint64_t nbad = t->bad_count[g].load(std::memory_order_acquire);
-    if (nbad == 0) {
+    if (t->bad_count[g].load(std::memory_order_acquire) == 0) continue;
+    const uint64_t gen = t->gpu_gen[g].load(std::memory_order_acquire);
+    if (!t->current_valid[g] || t->current_gen[g] != gen) stale.push_back(g);
+  }
+  auto rebuild = [t](uint32_t g) {
+    const uint64_t gen = t->gpu_gen[g].load(std::memory_order_acquire);
+    std::vector<uint8_t> &seg = t->current_seg[g];
+    seg.resize(t->unhealthy_size[g]);  // upper bound: every device unhealthy
+    uint8_t *end = encode_gpu(t, g, seg.data());
+    seg.resize((size_t)(end - seg.data()));
+    t->current_gen[g] = gen;
+    t->current_valid[g] = 1;
+  };
+  if (stale.size() > 1 && t->units >= 8192) {  // an event without a device takes every GPU down
+    std::vector<std::thread> pool;
+    const size_t workers = stale.size() < 8 ? stale.size() : 8;
+    for (size_t k = 0; k < workers; ++k)
+      pool.emplace_back([k, workers, &stale, &rebuild] {
+        for (size_t i = k; i < stale.size(); i += workers) rebuild(stale[i]);
+      });
+    for (auto &th : pool) th.join();
+  } else {
+    for (uint32_t g : stale) rebuild(g);
+  }
+  for (uint32_t g = 0; g < t->n_gpus; ++g) {
+    if (t->bad_count[g].load(std::memory_order_acquire) == 0) {
       iov[g].base = t->healthy_seg[g].data();
       iov[g].len = t->healthy_seg[g].size();
-      continue;
+    } else {
+      iov[g].base = t->current_seg[g].data();
+      iov[g].len = t->current_seg[g].size();
     }
-    const uint64_t gen = t->gpu_gen[g].load(std::memory_order_acquire);
-    if (!t->current_valid[g] || t->current_gen[g] != gen) {
-      std::vector<uint8_t> &seg = t->current_seg[g];
-      // upper bound: every device unhealthy
-      seg.resize(t->unhealthy_size[g]);
-      uint8_t *end = encode_gpu(t, g, seg.data());
-      seg.resize((size_t)(end - seg.data()));
-      t->current_gen[g] = gen;
-      t->current_valid[g] = 1;
-    }
-    iov[g].base = t->current_seg[g].data();
-    iov[g].len = t->current_seg[g].size();
   }
   return GS_OK;
 }
