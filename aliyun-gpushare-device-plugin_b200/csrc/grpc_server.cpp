@@ -38,6 +38,7 @@ using namespace gs_h2;
 
 namespace {
 
+constexpr uint64_t kSendSlice = 4u << 20;  // bytes of a device list per turn of the serving loop
 constexpr size_t kMaxStreams = 128;  // advertised in our SETTINGS and enforced
 enum Method { kUnknown, kOptions, kListAndWatch, kAllocate, kPreStart, kPreferred };
 const char kServicePrefix[] = "/v1beta1.DevicePlugin/";
@@ -179,6 +180,7 @@ struct gs_server {
   bool on_request_complete(Conn &c, Stream &s);
   bool flush(Conn &c, Stream &s);
   bool flush_all(Conn &c);
+  void continue_sends();
   bool send_error(Conn &c, Stream &s, int code, const std::string &msg);
   bool send_unary(Conn &c, Stream &s, const uint8_t *msg, size_t n);
   void close_stream(Conn &c, uint32_t id);
@@ -230,6 +232,10 @@ void gs_server::close_stream(Conn &c, uint32_t id) {
 bool gs_server::flush(Conn &c, Stream &s) {
   Outgoing &o = s.out;
   constexpr int kMaxFrames = 32;
+  // A device list can be tens of MB: it goes out in slices, and between slices the serving
+  // loop looks at its other streams and connections (continue_sends), so an Allocate never
+  // waits for a whole list to leave.
+  uint64_t budget = o.borrowed ? kSendSlice : ~0ull;
   for (;;) {
     std::vector<struct iovec> &iov = iov_scratch;
     iov.clear();
@@ -242,8 +248,9 @@ bool gs_server::flush(Conn &c, Stream &s) {
       iov.push_back({resp_headers.data(), resp_headers.size()});
       s.headers_sent = true;
     }
-    while (o.active && o.remaining && nfh < kMaxFrames) {
+    while (o.active && o.remaining && nfh < kMaxFrames && budget) {
       int64_t allow = (int64_t)o.remaining;
+      if ((uint64_t)allow > budget) allow = (int64_t)budget;
       if (allow > c.send_window) allow = c.send_window;
       if (allow > s.send_window) allow = s.send_window;
       if (allow > (int64_t)c.peer_max_frame) allow = c.peer_max_frame;
@@ -263,6 +270,7 @@ bool gs_server::flush(Conn &c, Stream &s) {
         }
       }
       o.remaining -= (uint64_t)allow;
+      budget -= (uint64_t)allow;
       c.send_window -= allow;
       s.send_window -= allow;
     }
@@ -285,7 +293,23 @@ bool gs_server::flush(Conn &c, Stream &s) {
       close_stream(c, s.id);
       return true;
     }
-    if (!(o.active && o.remaining && nfh >= kMaxFrames)) return true;
+    if (!(o.active && o.remaining && nfh >= kMaxFrames && budget)) return true;
+  }
+}
+
+// true when a stream of the connection has queued bytes the peer's windows would take now
+static bool sendable(const Conn &c) {
+  if (c.dead || c.send_window <= 0) return false;
+  for (const auto &kv : c.streams)
+    if (kv.second.out.active && kv.second.out.remaining && kv.second.send_window > 0) return true;
+  return false;
+}
+
+// one more slice of every suspended send
+void gs_server::continue_sends() {
+  for (auto &cp : conns) {
+    Conn &c = *cp;
+    if (sendable(c) && !flush_all(c)) c.dead = true;
   }
 }
 
@@ -877,10 +901,13 @@ void gs_server::run() {
     pfds.push_back({wake_fd, POLLIN, 0});
     pfds.push_back({listen_fd, POLLIN, 0});
     for (auto &c : conns) pfds.push_back({c->w.fd, POLLIN, 0});
-    const int r = poll(pfds.data(), (nfds_t)pfds.size(), 200);
+    bool pending = false;
+    for (auto &c : conns) pending = pending || sendable(*c);
+    const int r = poll(pfds.data(), (nfds_t)pfds.size(), pending ? 0 : 200);
     if (r < 0 && errno != EINTR) break;
     if (r <= 0) {
-      pump_law();  // a health change nobody announced with gs_plugin_notify_health
+      if (pending) continue_sends();
+      pump_law();  // also: a health change nobody announced with gs_plugin_notify_health
       continue;
     }
     const size_t n_conns = conns.size();  // accept_one may append
@@ -894,6 +921,7 @@ void gs_server::run() {
       if (pfds[2 + i].revents & (POLLIN | POLLHUP | POLLERR)) serve_conn(*conns[i]);
     }
     if (pfds[1].revents & POLLIN) accept_one();
+    if (pending) continue_sends();
     // health changed, a list finished (so a deferred one may start), or the plugin stopped
     pump_law();
     for (size_t i = 0; i < conns.size();) {
