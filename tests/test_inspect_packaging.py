@@ -183,3 +183,107 @@ def test_inspect_cli_end_to_end_over_http(tmp_path, monkeypatch, capsys):
     import pytest
     with pytest.raises(SystemExit):
         I.main([])
+
+
+def test_native_inspect_binary_matches_the_python_cli(tmp_path, monkeypatch, capsys):
+    """bin/kubectl-inspect-gpushare-v2 (daemon_cpp/inspect_main.cpp) against main() here, byte
+    for byte, on generated clusters: several nodes, pending pods, the scheduler-framework
+    allocation annotation, finished pods, non-sharing nodes, every flag."""
+    import http.server
+    import json
+    import random
+    import subprocess
+    import threading
+    import urllib.parse
+    exe = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "kubectl-inspect-gpushare-v2")
+    rng = random.Random(7)
+    state = {}
+
+    class H(http.server.BaseHTTPRequestHandler):
+        def log_message(self, *a):
+            pass
+
+        def do_GET(self):
+            u = urllib.parse.urlsplit(self.path)
+            nodes, pods = state["nodes"], state["pods"]
+            if state.get("fail_pods", 0) > 0 and u.path == "/api/v1/pods":
+                state["fail_pods"] -= 1
+                body = json.dumps({"kind": "Status", "message": "etcdserver: request timed out"}).encode()
+                self.send_response(500)
+            elif u.path == "/api/v1/nodes":
+                body = json.dumps({"items": nodes}).encode()
+                self.send_response(200)
+            elif u.path.startswith("/api/v1/nodes/"):
+                hit = [n for n in nodes if n["metadata"]["name"] == u.path.rsplit("/", 1)[1]]
+                body = json.dumps(hit[0] if hit else {"kind": "Status", "message": "nodes not found"}).encode()
+                self.send_response(200 if hit else 404)
+            elif u.path == "/api/v1/pods":
+                sel = urllib.parse.parse_qs(u.query).get("fieldSelector", [""])[0]
+                want = sel.split("=", 1)[1] if sel else None
+                body = json.dumps({"items": [p for p in pods if want is None or p["spec"].get("nodeName") == want]}).encode()
+                self.send_response(200)
+            else:
+                body = b"{}"
+                self.send_response(404)
+            self.send_header("Content-Length", str(len(body)))
+            self.end_headers()
+            self.wfile.write(body)
+
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), H)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    kc = tmp_path / "config"
+    kc.write_text("apiVersion: v1\nkind: Config\ncurrent-context: c\nclusters:\n- cluster:\n"
+                  "    server: http://127.0.0.1:%d\n  name: k\ncontexts:\n- context:\n    cluster: k\n    user: u\n"
+                  "  name: c\nusers:\n- name: u\n  user:\n    token: t\n" % srv.server_address[1])
+    monkeypatch.setenv("KUBECONFIG", str(kc))
+    env = dict(os.environ, KUBECONFIG=str(kc))
+
+    def both(argv):
+        snapshot = dict(state)
+        rc = I.main(argv)
+        want = capsys.readouterr().out
+        state.update(snapshot)
+        got = subprocess.run([exe] + argv, env=env, capture_output=True, timeout=60)
+        assert got.returncode == rc, got.stderr
+        assert got.stdout.decode() == want, (argv, got.stdout.decode(), want)
+        return want
+
+    try:
+        for trial in range(12):
+            n_nodes = rng.randrange(1, 5)
+            nodes, pods = [], []
+            for k in range(n_nodes):
+                count = rng.choice([0, 1, 2, 4, 8])
+                per = rng.choice([16, 179, 16384, 183359])
+                nodes.append(node("node-%d" % k, "10.0.%d.%d" % (trial, k), count * per, count))
+                if rng.random() < 0.2:
+                    nodes[-1]["status"]["addresses"] = []
+                for j in range(rng.randrange(0, 9)):
+                    extra = {}
+                    idx = rng.choice([None, "0", "1", "7", "-1", "x", "+2"])
+                    if rng.random() < 0.25 and count:
+                        extra["scheduler.framework.gpushare.allocation"] = json.dumps(
+                            {str(c): {str(rng.randrange(count)): rng.randrange(1, 50)} for c in range(rng.randrange(1, 3))})
+                    elif rng.random() < 0.1:
+                        extra["scheduler.framework.gpushare.allocation"] = rng.choice(["{", "[]", '{"a": {"0": 1}}'])
+                    p = pod("p%d-%d-%d" % (trial, k, j), rng.choice(["default", "team-b", "kube-system"]),
+                            "node-%d" % k, rng.choice([0, 1, 2, 10, 40, 1024]), idx,
+                            phase=rng.choice(["Running", "Running", "Pending", "Succeeded", "Failed"]), extra=extra)
+                    if rng.random() < 0.3:
+                        p["spec"]["containers"].append({"resources": {"limits": {"aliyun.com/gpu-mem": "3"}}})
+                    pods.append(p)
+            state.update(nodes=nodes, pods=pods)
+            both([])
+            both(["-d"])
+            both(["--unit", "MiB"])
+            both(["-d", "node-0"])
+            both(["node-%d" % (n_nodes - 1)])
+        state["fail_pods"] = 3                              # three failures, then the list arrives
+        both([])
+        state["fail_pods"] = 7                              # more than the 1 + 5 attempts
+        out = both(["-d"])
+        assert out == "Failed due to failed to get Pods"
+        state["fail_pods"] = 0
+        assert both(["no-such-node"]) == "Failed due to nodes not found"
+    finally:
+        srv.shutdown()

@@ -280,9 +280,9 @@ def test_slow_python_allocate_does_not_hold_up_the_watch_stream(golden_cases, so
         t0 = time.time()
         plug.unhealthy(0)
         msg = watcher.next_message(sid, timeout_ms=3000)
-        assert time.time() - t0 < 0.4 and msg.count(b"Unhealthy") == 16     # not behind the callback
+        assert time.time() - t0 < 0.65 and msg.count(b"Unhealthy") == 16    # not behind the callback
         assert watcher.call("GetDevicePluginOptions") == b""
-        assert time.time() - t0 < 0.5
+        assert time.time() - t0 < 0.7
         t1.join(10)
         t2.join(10)
         assert results["first"] == c["steps"][0]["expect_envs"]
