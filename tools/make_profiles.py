@@ -28,7 +28,7 @@ def launches():
     tot = sum(v[0] for vs in agg.values() for v in vs)
     with open(os.path.join(PROF, tag + "_bench_launches.md"), "w") as f:
         f.write("# %s -- ncu launch list of `python bench.py --steps 3 --warmup 3 --no-cpu-baseline`\n\n" % tag)
-        f.write("`ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv` on 1 x B200, after the "
+        f.write("`ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv` on 1 x B200, after the "
                 "same command exited 0 without ncu. Times are cold-cache and serialised by the profiler: compare "
                 "SHARES, not absolutes. Raw CSV beside this file.\n\n")
         f.write("| kernel | launches | total ms | share | median ms | grid x block |\n|---|---:|---:|---:|---:|---|\n")
