@@ -10,6 +10,7 @@
 // at 1024 units per GPU instead of 100 (a 179-GiB B200 is not "MiB"), --unit overrides it;
 // nodes keep the apiserver's order and devices go by index with pending (-1) last, where Go
 // iterates maps in random order.
+#include <signal.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -370,6 +371,7 @@ bool retry_get(const Transport &t, const std::string &path, JVal &out) {
 }  // namespace
 
 int main(int argc, char **argv) {
+  signal(SIGPIPE, SIG_IGN);  // a TLS peer that hangs up is an error message, not a death
   bool details = false;
   std::string unit, node_name;
   for (int i = 1; i < argc; ++i) {

@@ -27,21 +27,23 @@ md = """# profiles/ -- round 1 evidence
 All numbers from B200 boxes via `gpurun` (driver 580.159, CUDA 12.9), never under a profiler unless the
 file says ncu. The reference Go binary cannot be built on these machines; "reference model" is
 `oracle/ref_model.cpp`, the reference algorithm restated in C++ with its per-unit costs (conservative).
-Boxes differ a little (host CPU share, GPU sample): the 1-GPU line and the 2/4/8-GPU lines come from
-different calls, so compare within a call.
+Boxes differ a little (host CPU share, GPU sample); the four lines of the headline table come from one call on one
+8-GPU box, each the default command (100 steps, W = 3).
 
 ## Headline: `bench.py`, one process per GPU, MiB granularity (per-GPU shard of BASELINE configs[2]/[3])
 
-| GPUs | decisions/s (C ABI) | decisions/s (public API, e2e) | probe in step, per GPU | store / load | probe alone |
-|---:|---:|---:|---:|---|---:|
+| GPUs | decisions/s (C ABI) | decisions/s (public API, e2e) | decisions/s over the unix socket | probe in step, per GPU | store / load | probe alone |
+|---:|---:|---:|---:|---:|---|---:|
 """
 for n, v, e, a, w, r, al in rows:
-    md += "| %d | %.0f | %.0f | %.0f GB/s (%.0f%% of measured 6538, %.0f%% of nominal 8000) | %.0f / %.0f | %.0f GB/s |\n" % (
-        n, v, e, a, 100 * a / 6538.3, 100 * a / 8000, w, r, al)
+    sock = load("r01_bench_%dgpu.json" % n).get("over_socket", {}).get("value", 0)
+    md += "| %d | %.0f | %.0f | %.0f | %.0f GB/s (%.0f%% of measured 6538, %.0f%% of nominal 8000) | %.0f / %.0f | %.0f GB/s |\n" % (
+        n, v, e, sock, a, 100 * a / 6538.3, 100 * a / 8000, w, r, al)
 md += """
-A 200-step run of the same command (`r01_bench_1gpu_200steps.json`, timed region ~5 s per leg instead of ~0.2 s, so the
-end-of-run drain of the in-flight sweep is amortised and the board sits at its power cap): %.0f decisions/s at the
-C ABI, %.0f through the public API, probe %.0f GB/s in step.
+In these 100-step runs the board sits at its 1 kW power cap (`sw_power_cap` in `clocks.reasons`): the store pass holds
+~6.55 TB/s, the load pass ~7.3 TB/s. A timed region of a fraction of a second runs above that: an earlier 20-step set on
+an 8-GPU box measured 7.35 TB/s in step at every N, and a 200-step run (`r01_bench_1gpu_200steps.json`) %.0f decisions/s
+at the C ABI, %.0f through the public API, probe %.0f GB/s in step.
 
 The default command (`python bench.py`: 100 steps, W=3) on another box, with the over-the-socket leg
 (`r01_bench_1gpu_default.json`, `r01_bench_reference_1gpu_default.json`): %.0f decisions/s at the C ABI, %.0f through the
