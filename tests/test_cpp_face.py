@@ -2,7 +2,7 @@
 import os
 import subprocess
 
-from tests.conftest import CORE_SO, ROOT
+from tests.conftest import CORE_SO, ROOT, build_sanitized
 
 
 def test_cpp_consumer(tmp_path):
@@ -17,13 +17,7 @@ def test_cpp_consumer(tmp_path):
 def test_host_core_under_address_and_ub_sanitizers(tmp_path):
     """allocate/table/gosem/plugin/errors rebuilt with ASan + UBSan and driven with random
     tables, health marks, pods and (often malformed) requests: no out-of-bounds, overflow or leak."""
-    csrc = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc")
-    exe = tmp_path / "fuzz_core"
-    srcs = [os.path.join(csrc, f) for f in ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp")]
-    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
-                    "-I" + os.path.join(ROOT, "include"), "-I" + csrc,
-                    os.path.join(ROOT, "tests", "cpp", "fuzz_core.cpp")] + srcs + ["-o", str(exe), "-lpthread"],
-                   check=True)
+    exe = build_sanitized("asan", os.path.join(ROOT, "tests", "cpp", "fuzz_core.cpp"), tmp_path / "fuzz_core")
     out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "FUZZ CORE OK" in out.stdout, (out.stdout + out.stderr)[-3000:]
 
@@ -31,12 +25,7 @@ def test_host_core_under_address_and_ub_sanitizers(tmp_path):
 def test_host_core_under_thread_sanitizer(tmp_path):
     """Allocate from four threads, health marks, two ListAndWatch senders and the health wait, all
     on one table/plugin, under TSan: no data race."""
-    csrc = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc")
-    exe = tmp_path / "race_core"
-    srcs = [os.path.join(csrc, f) for f in ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp")]
-    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-I" + os.path.join(ROOT, "include"),
-                    "-I" + csrc, os.path.join(ROOT, "tests", "cpp", "race_core.cpp")] + srcs +
-                   ["-o", str(exe), "-lpthread"], check=True)
+    exe = build_sanitized("tsan", os.path.join(ROOT, "tests", "cpp", "race_core.cpp"), tmp_path / "race_core")
     out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "RACE CORE OK" in out.stdout and "WARNING: ThreadSanitizer" not in out.stderr, \
         (out.stdout + out.stderr)[-4000:]

@@ -412,21 +412,15 @@ def test_abi_argument_checks(sockdir):
     assert lib.gs_server_start(plug.h, C.byref(cfg), C.byref(h)) == L.GS_E_STATE
 
 
-def _build_transport_test(tmp_path, name, sanitize):
-    exe = str(tmp_path / name)
-    srcs = [os.path.join(CSRC, f) for f in ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp",
-                                             "grpc_server.cpp", "grpc_client.cpp")]
-    subprocess.run(["g++", "-std=c++17", "-O1", "-g"] + sanitize + ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC,
-                   os.path.join(ROOT, "tests", "cpp", "fuzz_transport.cpp")] + srcs + ["-o", exe, "-lpthread"],
-                   check=True)
-    return exe
+def _build_transport_test(tmp_path, name, kind):
+    from tests.conftest import build_sanitized
+    return build_sanitized(kind, os.path.join(ROOT, "tests", "cpp", "fuzz_transport.cpp"), tmp_path / name)
 
 
 def test_transport_fuzz_under_address_and_ub_sanitizers(tmp_path):
     """4000 mutated client sessions against a live server and 1000 mutated server sessions
     against the client, ASan + UBSan, with well-formed calls checked in between."""
-    exe = _build_transport_test(tmp_path, "fuzz_transport",
-                                ["-fsanitize=address,undefined", "-fno-sanitize-recover=all"])
+    exe = _build_transport_test(tmp_path, "fuzz_transport", "asan")
     out = subprocess.run([exe, "fuzz", "4000"], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "TRANSPORT FUZZ OK" in out.stdout, (out.stdout + out.stderr)[-3000:]
 
@@ -434,7 +428,7 @@ def test_transport_fuzz_under_address_and_ub_sanitizers(tmp_path):
 def test_transport_under_thread_sanitizer(tmp_path):
     """Two Allocate callers, a ListAndWatch reader, a health marker and Stop at once: no race,
     and the watch stream ends with status OK."""
-    exe = _build_transport_test(tmp_path, "race_transport", ["-fsanitize=thread"])
+    exe = _build_transport_test(tmp_path, "race_transport", "tsan")
     out = subprocess.run([exe, "race", "2"], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "TRANSPORT RACE OK" in out.stdout \
         and "WARNING: ThreadSanitizer" not in out.stderr, (out.stdout + out.stderr)[-4000:]
