@@ -510,3 +510,39 @@ def test_frames_grpc_core_never_sends(golden_cases, sockdir):
         assert goaway and int.from_bytes(goaway[0][4:8], "big") == 1                        # PROTOCOL_ERROR
     finally:
         srv.Stop()
+
+
+def test_kubelet_dials_back_inside_register(golden_cases, sockdir):
+    """kubelet's Register handler connects to the plugin's socket (blocking dial,
+    GetDevicePluginOptions) before it answers; the plugin must be serving while its own
+    Register call is still outstanding (server.go:240-244 registers after Start for that reason)."""
+    from concurrent import futures
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    plugin_sock = os.path.join(sockdir, "aliyungpushare.sock")
+    seen = {}
+
+    def register(request, context):
+        ch = grpc.insecure_channel("unix://" + plugin_sock)
+        grpc.channel_ready_future(ch).result(timeout=5)
+        seen["options"] = KubeletStub.method(ch, "GetDevicePluginOptions")(b"", timeout=5)
+        stream = KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")
+        seen["devices"] = len(R.decode_list_and_watch(next(stream)))
+        stream.cancel()
+        ch.close()
+        seen["request"] = request
+        return b""
+    kubelet = grpc.server(futures.ThreadPoolExecutor(max_workers=2))
+    kubelet.add_generic_rpc_handlers((grpc.method_handlers_generic_handler("v1beta1.Registration", {
+        "Register": grpc.unary_unary_rpc_method_handler(register, lambda b: b, lambda b: b)}),))
+    kubelet_sock = os.path.join(sockdir, "kubelet.sock")
+    kubelet.add_insecure_port("unix://" + kubelet_sock)
+    kubelet.start()
+    srv = NativeDevicePluginServer(plug, plugin_sock)
+    try:
+        srv.Serve(kubelet_sock)
+        assert seen["options"] == b"" and seen["devices"] == 128
+        assert seen["request"] == encode_register_request("v1beta1", "aliyungpushare.sock", "aliyun.com/gpu-mem")
+    finally:
+        srv.Stop()
+        kubelet.stop(grace=0)
