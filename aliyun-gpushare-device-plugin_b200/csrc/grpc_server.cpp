@@ -450,6 +450,11 @@ bool gs_server::on_headers_complete(Conn &c, uint32_t id, uint8_t flags) {
       c.w.send_goaway(c.last_stream, kErrProtocol);
       return false;
     }
+    if (!it->second.req) {  // the request was complete already (half-closed): RFC 7540 5.1
+      c.w.send_rst(id, kErrStreamClosed);
+      close_stream(c, id);
+      return true;
+    }
     return on_request_complete(c, it->second);
   }
   if (id <= c.last_stream) return true;  // headers of a stream already closed: ignore

@@ -122,7 +122,7 @@ static size_t throw_at_server(const std::string &sock, const std::vector<uint8_t
 }
 
 static void mutate(std::vector<uint8_t> &b, std::mt19937 &rng) {
-  const int kind = (int)(rng() % 7);
+  const int kind = (int)(rng() % 9);
   if (b.empty()) return;
   switch (kind) {
     case 0:  // flip a few bytes anywhere
@@ -155,6 +155,19 @@ static void mutate(std::vector<uint8_t> &b, std::mt19937 &rng) {
       const size_t from = b.size() > 33 ? 33 : 0;
       std::vector<uint8_t> tail(b.begin() + (long)from, b.end());
       b.insert(b.end(), tail.begin(), tail.end());
+      break;
+    }
+    case 6: {  // a late header block (END_STREAM) on a stream whose request is already complete
+      std::vector<uint8_t> block;
+      encode_literal(block, "x-late", 6, "trailer", 7);
+      frame(b, kHeaders, kFlagEndHeaders | kFlagEndStream, (uint32_t)(1 + 2 * (rng() % 3)), block);
+      break;
+    }
+    case 7: {  // DATA / WINDOW_UPDATE / RST_STREAM for streams in every state
+      std::vector<uint8_t> payload(4 + rng() % 8);
+      for (auto &x : payload) x = (uint8_t)rng();
+      const uint8_t types[3] = {kData, kWindowUpdate, kRstStream};
+      frame(b, types[rng() % 3], (uint8_t)(rng() % 2), (uint32_t)(rng() % 8), payload);
       break;
     }
     default:  // append garbage

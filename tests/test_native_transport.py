@@ -508,6 +508,24 @@ def test_frames_grpc_core_never_sends(golden_cases, sockdir):
         s.close()
         goaway = [p for t, f, sid, p in frames if t == 7]
         assert goaway and int.from_bytes(goaway[0][4:8], "big") == 1                        # PROTOCOL_ERROR
+        # trailers on a stream whose request is already complete (an open watch stream): a stream
+        # error, and the connection keeps serving
+        law = b"\x83\x86" + b"\x04" + bytes([len(b"/v1beta1.DevicePlugin/ListAndWatch")]) + \
+            b"/v1beta1.DevicePlugin/ListAndWatch" + _lit(b"content-type", b"application/grpc")
+        opts = b"\x83\x86" + b"\x04" + bytes([len(b"/v1beta1.DevicePlugin/GetDevicePluginOptions")]) + \
+            b"/v1beta1.DevicePlugin/GetDevicePluginOptions" + _lit(b"content-type", b"application/grpc")
+        s = pysock.socket(pysock.AF_UNIX, pysock.SOCK_STREAM)
+        s.settimeout(5)
+        s.connect(srv.socket)
+        s.sendall(b"PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n" + _frame(4, 0, 0)
+                  + _frame(1, 0x04, 1, law) + _frame(0, 0x01, 1, b"\x00\x00\x00\x00\x00")
+                  + _frame(1, 0x04 | 0x01, 1, _lit(b"x-late", b"trailer"))
+                  + _frame(1, 0x04, 3, opts) + _frame(0, 0x01, 3, b"\x00\x00\x00\x00\x00"))
+        s.shutdown(pysock.SHUT_WR)
+        frames = _read_frames(s)
+        s.close()
+        assert any(t == 3 and sid == 1 and int.from_bytes(p, "big") == 5 for t, f, sid, p in frames)   # STREAM_CLOSED
+        assert any(t == 1 and sid == 3 and p.endswith(b"\x0bgrpc-status\x010") for t, f, sid, p in frames)
     finally:
         srv.Stop()
 
