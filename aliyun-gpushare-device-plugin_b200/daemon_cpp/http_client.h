@@ -6,6 +6,7 @@
 #include <errno.h>
 #include <netdb.h>
 #include <openssl/err.h>
+#include <openssl/pem.h>
 #include <openssl/ssl.h>
 #include <openssl/x509v3.h>
 #include <stdio.h>
@@ -28,6 +29,7 @@ struct HttpResponse {
 
 struct TlsOptions {
   std::string ca_file, cert_file, key_file;
+  std::string ca_pem, cert_pem, key_pem;  // the same three inline (kubeconfig *-data fields, decoded)
   bool insecure = false;  // skip verification (the kubelet client always does, main.go:41)
 };
 
@@ -208,11 +210,25 @@ inline bool http_request(const std::string &base_url, const std::string &method,
       err = detail::ssl_error();
       return false;
     }
-    const bool verify = !tls.insecure && !tls.ca_file.empty();
+    const bool verify = !tls.insecure && (!tls.ca_file.empty() || !tls.ca_pem.empty());
     if (verify) {
-      if (SSL_CTX_load_verify_locations(s.ctx, tls.ca_file.c_str(), nullptr) != 1) {
+      if (!tls.ca_file.empty() && SSL_CTX_load_verify_locations(s.ctx, tls.ca_file.c_str(), nullptr) != 1) {
         err = "unable to load CA file " + tls.ca_file + ": " + detail::ssl_error();
         return false;
+      }
+      if (!tls.ca_pem.empty()) {
+        BIO *bio = BIO_new_mem_buf(tls.ca_pem.data(), (int)tls.ca_pem.size());
+        int added = 0;
+        while (X509 *x = PEM_read_bio_X509(bio, nullptr, nullptr, nullptr)) {
+          added += X509_STORE_add_cert(SSL_CTX_get_cert_store(s.ctx), x) == 1;
+          X509_free(x);
+        }
+        BIO_free(bio);
+        ERR_clear_error();  // the read that found the end of the bundle
+        if (!added) {
+          err = "certificate-authority-data holds no certificate";
+          return false;
+        }
       }
       SSL_CTX_set_verify(s.ctx, SSL_VERIFY_PEER, nullptr);
     } else {
@@ -222,6 +238,20 @@ inline bool http_request(const std::string &base_url, const std::string &method,
       if (SSL_CTX_use_certificate_chain_file(s.ctx, tls.cert_file.c_str()) != 1 ||
           SSL_CTX_use_PrivateKey_file(s.ctx, tls.key_file.c_str(), SSL_FILETYPE_PEM) != 1) {
         err = "unable to load client certificate: " + detail::ssl_error();
+        return false;
+      }
+    } else if (!tls.cert_pem.empty() && !tls.key_pem.empty()) {
+      BIO *cb = BIO_new_mem_buf(tls.cert_pem.data(), (int)tls.cert_pem.size());
+      BIO *kb = BIO_new_mem_buf(tls.key_pem.data(), (int)tls.key_pem.size());
+      X509 *x = PEM_read_bio_X509(cb, nullptr, nullptr, nullptr);
+      EVP_PKEY *k = PEM_read_bio_PrivateKey(kb, nullptr, nullptr, nullptr);
+      const bool ok = x && k && SSL_CTX_use_certificate(s.ctx, x) == 1 && SSL_CTX_use_PrivateKey(s.ctx, k) == 1;
+      if (x) X509_free(x);
+      if (k) EVP_PKEY_free(k);
+      BIO_free(cb);
+      BIO_free(kb);
+      if (!ok) {
+        err = "unable to load client-certificate-data / client-key-data: " + detail::ssl_error();
         return false;
       }
     }

@@ -45,6 +45,28 @@ inline std::string trim(std::string s) {
   return s.substr(i);
 }
 
+inline std::string base64_decode(const std::string &in) {
+  std::string out;
+  uint32_t acc = 0;
+  int bits = 0;
+  for (unsigned char ch : in) {
+    int v;
+    if (ch >= 'A' && ch <= 'Z') v = ch - 'A';
+    else if (ch >= 'a' && ch <= 'z') v = ch - 'a' + 26;
+    else if (ch >= '0' && ch <= '9') v = ch - '0' + 52;
+    else if (ch == '+' || ch == '-') v = 62;
+    else if (ch == '/' || ch == '_') v = 63;
+    else continue;  // padding, whitespace
+    acc = acc << 6 | (uint32_t)v;
+    bits += 6;
+    if (bits >= 8) {
+      bits -= 8;
+      out.push_back((char)(acc >> bits & 0xff));
+    }
+  }
+  return out;
+}
+
 // Where the apiserver is and how to authenticate (kubeInit, podmanager.go:32-53).
 struct ApiConfig {
   std::string host, token;
@@ -72,8 +94,10 @@ struct ApiConfig {
     return true;
   }
 
-  // A kubeconfig with one cluster, one user, one context (what `kubectl config view --minify`
-  // prints): the keys are taken where they first appear. Inline *-data forms are not read.
+  // A kubeconfig with one cluster, one user, one context (what `kubectl config view --minify
+  // --raw` prints, and what kubeadm writes as kubelet.conf, the file the reference DaemonSet
+  // points KUBECONFIG at, device-plugin-ds.yaml:41-47): the keys are taken where they first
+  // appear, block style. Inline *-data fields (base64 PEM) are read as well as the file forms.
   static bool from_kubeconfig(const std::string &path, ApiConfig &c, std::string &err) {
     std::string text;
     if (!read_file(path, text)) {
@@ -103,6 +127,9 @@ struct ApiConfig {
     c.tls.cert_file = first("client-certificate");
     c.tls.key_file = first("client-key");
     c.tls.insecure = first("insecure-skip-tls-verify") == "true";
+    c.tls.ca_pem = base64_decode(first("certificate-authority-data"));
+    c.tls.cert_pem = base64_decode(first("client-certificate-data"));
+    c.tls.key_pem = base64_decode(first("client-key-data"));
     if (c.host.empty()) {
       err = "no cluster server in " + path;
       return false;

@@ -48,10 +48,11 @@ class ListerError(Exception):
 class ApiConfig:
     """Where the apiserver is and how to authenticate (kubeInit, podmanager.go:32-53)."""
 
-    def __init__(self, host, token="", ca_file=None, cert_file=None, key_file=None, insecure=False):
+    def __init__(self, host, token="", ca_file=None, cert_file=None, key_file=None, insecure=False, ca_data=None):
         self.host = host.rstrip("/")
         self.token = token
         self.ca_file, self.cert_file, self.key_file, self.insecure = ca_file, cert_file, key_file, insecure
+        self.ca_data = ca_data                    # PEM text of certificate-authority-data
 
     @classmethod
     def load(cls):
@@ -82,17 +83,36 @@ class ApiConfig:
         ctx = next(c["context"] for c in doc.get("contexts", []) if c["name"] == ctx_name)
         cluster = next(c["cluster"] for c in doc.get("clusters", []) if c["name"] == ctx["cluster"])
         user = next((u["user"] for u in doc.get("users", []) if u["name"] == ctx.get("user")), {})
+        # inline *-data fields (kubeadm's kubelet.conf, which the reference DaemonSet points
+        # KUBECONFIG at, device-plugin-ds.yaml:41-47): the CA stays in memory, a client key pair
+        # has to be a file for ssl.load_cert_chain
+        import base64
+        import tempfile
+
+        def as_file(data):
+            f = tempfile.NamedTemporaryFile(prefix="gs-kubeconfig-", suffix=".pem", delete=False)
+            f.write(base64.b64decode(data))
+            f.close()
+            os.chmod(f.name, 0o600)
+            return f.name
+        cert_file, key_file = user.get("client-certificate"), user.get("client-key")
+        if not cert_file and user.get("client-certificate-data") and user.get("client-key-data"):
+            cert_file, key_file = as_file(user["client-certificate-data"]), as_file(user["client-key-data"])
+        ca_data = cluster.get("certificate-authority-data")
         return cls(cluster["server"], user.get("token", ""), ca_file=cluster.get("certificate-authority"),
-                   cert_file=user.get("client-certificate"), key_file=user.get("client-key"),
-                   insecure=bool(cluster.get("insecure-skip-tls-verify")))
+                   cert_file=cert_file, key_file=key_file,
+                   insecure=bool(cluster.get("insecure-skip-tls-verify")),
+                   ca_data=base64.b64decode(ca_data).decode() if ca_data else None)
 
 
-def _connection(url, timeout, ca_file=None, cert_file=None, key_file=None, insecure=False):
+def _connection(url, timeout, ca_file=None, cert_file=None, key_file=None, insecure=False, ca_data=None):
     u = urllib.parse.urlsplit(url)
     if u.scheme == "http":
         return http.client.HTTPConnection(u.hostname, u.port or 80, timeout=timeout), u
-    ctx = ssl.create_default_context(cafile=ca_file) if (ca_file and not insecure) else ssl.create_default_context()
-    if insecure or not ca_file:
+    have_ca = bool(ca_file or ca_data)
+    ctx = (ssl.create_default_context(cafile=ca_file, cadata=ca_data) if (have_ca and not insecure)
+           else ssl.create_default_context())
+    if insecure or not have_ca:
         ctx.check_hostname = False
         ctx.verify_mode = ssl.CERT_NONE
     if cert_file and key_file:
@@ -115,7 +135,7 @@ class HttpTransport:
         if self.api is None:
             raise ApiError("no apiserver configured")
         conn, _u = _connection(self.api.host, self.timeout, self.api.ca_file, self.api.cert_file,
-                               self.api.key_file, self.api.insecure)
+                               self.api.key_file, self.api.insecure, getattr(self.api, "ca_data", None))
         headers = {"Accept": "application/json"}
         if self.api.token:
             headers["Authorization"] = "Bearer " + self.api.token

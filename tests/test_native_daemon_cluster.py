@@ -91,7 +91,8 @@ def _strip_time(pods):
 class Rig:
     """fake cluster over HTTP + kubelet registration stub + the binary."""
 
-    def __init__(self, d, script, query_kubelet, gpus=8, labels=None, capacity=None, tls=None, ca_line=""):
+    def __init__(self, d, script, query_kubelet, gpus=8, labels=None, capacity=None, tls=None, ca_line="",
+                 user_lines="", client_ca=None):
         self.cluster = FakeCluster(PODS, script)
         self.handler = type("H", (Handler,), {"cluster": self.cluster, "node_gets": 0, "node_patches": [],
                                               "labels": labels or {}, "capacity": capacity or {}})
@@ -100,6 +101,9 @@ class Rig:
             import ssl
             ctx = ssl.SSLContext(ssl.PROTOCOL_TLS_SERVER)
             ctx.load_cert_chain(*tls)
+            if client_ca:                              # mutual TLS: the apiserver wants a client certificate
+                ctx.verify_mode = ssl.CERT_REQUIRED
+                ctx.load_verify_locations(client_ca)
             self.http.socket = ctx.wrap_socket(self.http.socket, server_side=True)
         threading.Thread(target=self.http.serve_forever, daemon=True).start()
         base = "%s://127.0.0.1:%d" % ("https" if tls else "http", self.http.server_address[1])
@@ -107,7 +111,7 @@ class Rig:
         with open(kc, "w") as f:                       # as `kubectl config view --minify` prints it
             f.write("apiVersion: v1\nkind: Config\ncurrent-context: c\nclusters:\n- cluster:\n%s    server: %s\n"
                     "  name: k\ncontexts:\n- context:\n    cluster: k\n    user: u\n  name: c\nusers:\n- name: u\n"
-                    "  user:\n    token: tok\n" % (ca_line, base))
+                    "  user:\n    token: tok\n%s" % (ca_line, base, user_lines))
         self.kubelet = KubeletStub(os.path.join(d, "kubelet.sock"))
         self.kubelet.start()
         env = dict(os.environ, NODE_NAME="node-a", FAKE_NVML_GPUS=str(gpus), FAKE_NVML_MEM_MIB="16384",
@@ -241,6 +245,43 @@ def test_binary_over_tls():
         finally:
             rig.close()
         assert rig.proc.returncode == 0
+
+
+def test_binary_reads_inline_kubeconfig_credentials():
+    """kubeadm's kubelet.conf (what the reference DaemonSet mounts as KUBECONFIG,
+    device-plugin-ds.yaml:41-47) carries its CA and client key pair inline as base64 *-data
+    fields: the CA is honoured (a wrong one stops the daemon), the key pair is presented."""
+    import base64
+    with tempfile.TemporaryDirectory(prefix="gsc") as d:
+        server, client, other = _self_signed(d, "server"), _self_signed(d, "client"), _self_signed(d, "stranger")
+        b64 = lambda path: base64.b64encode(open(path, "rb").read()).decode()
+        user = "    client-certificate-data: %s\n    client-key-data: %s\n" % (b64(client[0]), b64(client[1]))
+        rig = Rig(d, {}, False, tls=server, ca_line="    certificate-authority-data: %s\n" % b64(server[0]),
+                  user_lines=user, client_ca=client[0], capacity={"aliyun.com/gpu-count": "8"})
+        try:
+            assert rig.kubelet.wait_registered(30), rig.proc.stderr.read() if rig.proc.poll() is not None else ""
+            with NativeClient(rig.sock) as cl:
+                envs = R.decode_allocate_response(cl.call("Allocate", R.encode_allocate_request([["x", "y"]])))
+            assert envs[0]["ALIYUN_COM_GPU_MEM_IDX"] == "2"
+            # the Python host reads the same file the same way and gets through the same door
+            from gpushare_b200 import k8s_io
+            cfg = k8s_io.ApiConfig.from_kubeconfig(os.path.join(d, "kubeconfig"))
+            assert "BEGIN CERTIFICATE" in cfg.ca_data and open(cfg.cert_file).read() == open(client[0]).read()
+            node = k8s_io.HttpTransport(cfg, timeout=5).get_node("node-a")
+            assert node["status"]["capacity"] == {"aliyun.com/gpu-count": "8"}
+            os.remove(cfg.cert_file), os.remove(cfg.key_file)
+        finally:
+            rig.close()
+        assert rig.proc.returncode == 0
+    with tempfile.TemporaryDirectory(prefix="gsc") as d:
+        server, other = _self_signed(d, "server"), _self_signed(d, "stranger")
+        rig = Rig(d, {}, False, tls=server,
+                  ca_line="    certificate-authority-data: %s\n" % base64.b64encode(open(other[0], "rb").read()).decode())
+        try:
+            assert rig.proc.wait(30) == 1
+            assert "certificate verify failed" in rig.proc.stderr.read()
+        finally:
+            rig.close()
 
 
 def test_binary_exit_codes():
