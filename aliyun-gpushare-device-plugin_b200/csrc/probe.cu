@@ -56,51 +56,56 @@ struct DevResult {
   unsigned long long reserved;
 };
 
-// pattern(i, seed): i = index of the 16-byte word inside the slice. Every output
-// word depends on every bit of i and of seed; word 1 is the complement of word 0
-// so each bit position is exercised in both polarities. Restated on the CPU in
-// oracle/pattern.c (test infrastructure only).
+// pattern(i, seed): i = index of the 16-byte word inside the slice.
+//
+//   background(seed) = four 32-bit words r0..r3 drawn once per sweep from the seed
+//   word(i)          = { r0 ^ lo(i), r1 ^ hi(i), r2, r3 }
+//
+// Every cell holds a pseudo-random bit that changes with the seed (both polarities over
+// successive sweeps; a stale sweep never matches), and every 16-byte word carries its own
+// address, so aliased, shifted, dropped or zeroed words all mismatch. What the pattern
+// deliberately does NOT do is change many bits from one word to the next: under the board's
+// power cap the store pass is priced by how many bits toggle between the transfers that
+// different SMs interleave on the shared path to HBM. A per-word avalanche hash (the first
+// version of this pattern) sustains 6.6 TB/s of stores; this form, which toggles ~8 bits per
+// 128, sustains 7.2 TB/s (tools/exp/write_entropy9.cu, profiles/r01_write_entropy.txt).
+// Restated on the CPU in oracle/pattern.c (test infrastructure only).
+struct Background {
+  uint32_t r0, r1, r2, r3;
+};
+__device__ __forceinline__ Background slice_background(uint32_t seed) {
+  uint32_t r = seed * 0x9E3779B1u + 0x7F4A7C15u;
+  r ^= r >> 15;
+  r *= 0x2C1B3C6Du;
+  r ^= r >> 12;
+  Background b;
+  b.r0 = r;
+  b.r1 = b.r0 * 0x85EBCA77u + 1u;
+  b.r2 = b.r1 * 0xC2B2AE3Du + 1u;
+  b.r3 = b.r2 * 0x27D4EB2Fu + 1u;
+  return b;
+}
 __device__ __forceinline__ uint4 slice_pattern(uint64_t i, uint32_t seed) {
-  const uint32_t lo = (uint32_t)i;
-  const uint32_t hi = (uint32_t)(i >> 32);
-  uint32_t h = lo * 0x9E3779B1u + (hi ^ seed) * 0x85EBCA77u + seed;
-  h ^= h >> 15;
-  h *= 0x2C1B3C6Du;
-  h ^= h >> 12;
-  uint4 v;
-  v.x = h;
-  v.y = ~h;
-  v.z = h * 0x297A2D39u + lo;
-  v.w = __funnelshift_l(h, h, 13) ^ hi ^ 0xC2B2AE3Du;
-  return v;
+  const Background b = slice_background(seed);
+  return make_uint4(b.r0 ^ (uint32_t)i, b.r1 ^ (uint32_t)(i >> 32), b.r2, b.r3);
 }
 
-// The same function, split for the kernels' inner loops: a tile is 4096 words and starts
-// on a multiple of 4096, so the high index word and everything derived from it and the
-// seed are constant across a tile and are folded once per tile; per word one multiply-add,
-// the avalanche, and the three derived words remain. Bit-identical to slice_pattern.
+// The same function, split for the kernels' inner loops: a tile is 4096 words and starts on
+// a multiple of 4096, so the background and the high index word are folded once per tile and
+// one add and one xor per word remain. Bit-identical to slice_pattern.
 struct TilePattern {
-  uint32_t base;  // (hi ^ seed) * 0x85EBCA77 + seed
-  uint32_t hic;   // hi ^ 0xC2B2AE3D
-  uint32_t lo0;   // low index word of the tile's first word
+  uint32_t r0, y, z, w;  // y = r1 ^ hi; z, w = r2, r3
+  uint32_t lo0;          // low index word of the tile's first word
   __device__ __forceinline__ TilePattern(uint64_t v0, uint32_t seed) {
-    const uint32_t hi = (uint32_t)(v0 >> 32);
-    base = (hi ^ seed) * 0x85EBCA77u + seed;
-    hic = hi ^ 0xC2B2AE3Du;
+    const Background b = slice_background(seed);
+    r0 = b.r0;
+    y = b.r1 ^ (uint32_t)(v0 >> 32);
+    z = b.r2;
+    w = b.r3;
     lo0 = (uint32_t)v0;
   }
   __device__ __forceinline__ uint4 word(uint32_t j) const {  // j < kTileVec
-    const uint32_t lo = lo0 + j;
-    uint32_t h = lo * 0x9E3779B1u + base;
-    h ^= h >> 15;
-    h *= 0x2C1B3C6Du;
-    h ^= h >> 12;
-    uint4 v;
-    v.x = h;
-    v.y = ~h;
-    v.z = h * 0x297A2D39u + lo;
-    v.w = __funnelshift_l(h, h, 13) ^ hic;
-    return v;
+    return make_uint4(r0 ^ (lo0 + j), y, z, w);
   }
 };
 

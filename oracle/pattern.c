@@ -17,20 +17,28 @@
 #include <stddef.h>
 #include <stdint.h>
 
-static inline uint32_t rotl32(uint32_t x, unsigned r) { return (x << r) | (x >> (32u - r)); }
+/* background(seed): four 32-bit words drawn once per sweep. */
+static void background(uint32_t seed, uint32_t r[4]) {
+  uint32_t x = seed * 0x9E3779B1u + 0x7F4A7C15u;
+  x ^= x >> 15;
+  x *= 0x2C1B3C6Du;
+  x ^= x >> 12;
+  r[0] = x;
+  r[1] = r[0] * 0x85EBCA77u + 1u;
+  r[2] = r[1] * 0xC2B2AE3Du + 1u;
+  r[3] = r[2] * 0x27D4EB2Fu + 1u;
+}
 
-/* Four little-endian 32-bit words of the 16-byte pattern word i. */
+/* Four little-endian 32-bit words of the 16-byte pattern word i:
+ * { r0 ^ lo(i), r1 ^ hi(i), r2, r3 } -- a per-sweep random background with the word's
+ * address in it (why this shape: csrc/probe.cu). */
 void gs_oracle_pattern_word(uint64_t i, uint32_t seed, uint32_t out[4]) {
-  const uint32_t lo = (uint32_t)i;
-  const uint32_t hi = (uint32_t)(i >> 32);
-  uint32_t h = lo * 0x9E3779B1u + (hi ^ seed) * 0x85EBCA77u + seed;
-  h ^= h >> 15;
-  h *= 0x2C1B3C6Du;
-  h ^= h >> 12;
-  out[0] = h;
-  out[1] = ~h;
-  out[2] = h * 0x297A2D39u + lo;
-  out[3] = rotl32(h, 13) ^ hi ^ 0xC2B2AE3Du;
+  uint32_t r[4];
+  background(seed, r);
+  out[0] = r[0] ^ (uint32_t)i;
+  out[1] = r[1] ^ (uint32_t)(i >> 32);
+  out[2] = r[2];
+  out[3] = r[3];
 }
 
 /* Fill n_words 16-byte words starting at word index first. */

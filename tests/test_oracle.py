@@ -29,8 +29,25 @@ def test_pattern_kat(oracle_lib, pattern_kat):
         w = (ctypes.c_uint32 * 4)()
         oracle_lib.gs_oracle_pattern_word(ctypes.c_uint64(v["i"]), ctypes.c_uint32(v["seed"]), w)
         assert list(w) == v["words"]
-    # first vector by hand: i = 0, seed = 0 => h = 0 through the whole mix
-    assert pattern_kat[0]["words"] == [0, 0xFFFFFFFF, 0, 0xC2B2AE3D]
+    # an independent restatement of the written definition (csrc/probe.cu):
+    # background(seed) = r0..r3, word(i) = {r0 ^ lo(i), r1 ^ hi(i), r2, r3}
+    M = 0xFFFFFFFF
+
+    def background(seed):
+        x = (seed * 0x9E3779B1 + 0x7F4A7C15) & M
+        x ^= x >> 15
+        x = (x * 0x2C1B3C6D) & M
+        x ^= x >> 12
+        r1 = (x * 0x85EBCA77 + 1) & M
+        r2 = (r1 * 0xC2B2AE3D + 1) & M
+        return x, r1, r2, (r2 * 0x27D4EB2F + 1) & M
+    assert background(0) == (0x98E34241, 0xFA961638, 0x9BCD5B59, 0x52427858)       # by hand
+    for v in pattern_kat:
+        r = background(v["seed"])
+        assert v["words"] == [r[0] ^ (v["i"] & M), r[1] ^ (v["i"] >> 32), r[2], r[3]]
+    assert pattern_kat[0]["words"] == [0x98E34241, 0xFA961638, 0x9BCD5B59, 0x52427858]   # i = 0, seed = 0
+    # every word of a sweep carries its own address; a different seed changes every lane
+    assert len({tuple(v["words"]) for v in pattern_kat}) == len(pattern_kat)
 
 
 def test_oracle_pattern_check_counts(oracle_lib):

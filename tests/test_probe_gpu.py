@@ -186,10 +186,10 @@ def test_health_time_sweep_of_free_memory(probe):
     assert tm.bytes > 100 << 30 and tm.gbps() > 5000       # most of a B200, at HBM speed
 
 
-def test_full_size_properties_40gib(probe):
-    """BASELINE config 4's largest tenant (40 GiB), no oracle needed: a sweep is clean; read back
-    under another seed EVERY word differs and about half of all bits flip (the pattern is a hash);
-    one flipped bit anywhere is found at its exact byte."""
+def test_full_size_properties_40gib(probe, oracle_lib):
+    """BASELINE config 4's largest tenant (40 GiB): a sweep is clean; read back under another
+    seed EVERY word differs, by exactly the bits in which the two sweeps' backgrounds differ (the
+    address terms cancel); one flipped bit anywhere is found at its exact byte."""
     nbytes = 40 << 30
     free, _ = probe.mem_info()
     if free < nbytes + (2 << 30):
@@ -200,7 +200,13 @@ def test_full_size_properties_40gib(probe):
         assert v[0].clean and tm.bytes == nbytes
         w, _ = probe.run([(d, nbytes, 0x5A5A)], L.GS_PROBE_VERIFY)
         assert w[0].mismatches == nbytes // 16 and w[0].first_bad_byte == 0
-        assert 0.49 < w[0].bit_flips / (nbytes * 8) < 0.51
+        import ctypes
+        a, b = (ctypes.c_uint32 * 4)(), (ctypes.c_uint32 * 4)()
+        oracle_lib.gs_oracle_pattern_word(ctypes.c_uint64(0), ctypes.c_uint32(0xA5A5), a)
+        oracle_lib.gs_oracle_pattern_word(ctypes.c_uint64(0), ctypes.c_uint32(0x5A5A), b)
+        per_word = sum(bin(x ^ y).count("1") for x, y in zip(a, b))
+        assert 32 < per_word < 96                      # two backgrounds: about half of 128 bits
+        assert w[0].bit_flips == per_word * (nbytes // 16)
         off = (37 << 30) + 4 * 12345
         probe.inject(d, off, 1 << 9)
         v, _ = probe.run([(d, nbytes, 0xA5A5)], L.GS_PROBE_VERIFY)
