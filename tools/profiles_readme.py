@@ -40,10 +40,11 @@ for n, v, e, a, w, r, al in rows:
     md += "| %d | %.0f | %.0f | %.0f | %.0f GB/s (%.0f%% of measured 6538, %.0f%% of nominal 8000) | %.0f / %.0f | %.0f GB/s |\n" % (
         n, v, e, sock, a, 100 * a / 6538.3, 100 * a / 8000, w, r, al)
 md += """
-In these 100-step runs the board sits at its 1 kW power cap (`sw_power_cap` in `clocks.reasons`): the store pass holds
-~6.55 TB/s, the load pass ~7.3 TB/s. A timed region of a fraction of a second runs above that: an earlier 20-step set on
-an 8-GPU box measured 7.35 TB/s in step at every N, and a 200-step run (`r01_bench_1gpu_200steps.json`) %.0f decisions/s
-at the C ABI, %.0f through the public API, probe %.0f GB/s in step.
+The probe rate no longer depends on the length of the timed region: with the background+address pattern the store pass
+runs below the 1 kW cap (`r01_write_entropy.txt`, DESIGN.md section 4). With the first, hashed pattern the same kernels held
+6.90 TB/s in a 100-step run (store 6.55, load 7.30, `sw_power_cap` active) and 7.35 TB/s only in sub-second regions.
+A 200-step run (`r01_bench_1gpu_200steps.json`): %.0f decisions/s at the C ABI, %.0f through the public API, probe
+%.0f GB/s in step.
 
 The default command (`python bench.py`: 100 steps, W=3) on another box, with the over-the-socket leg
 (`r01_bench_1gpu_default.json`, `r01_bench_reference_1gpu_default.json`): %.0f decisions/s at the C ABI, %.0f through the
