@@ -564,3 +564,59 @@ def test_kubelet_dials_back_inside_register(golden_cases, sockdir):
     finally:
         srv.Stop()
         kubelet.stop(grace=0)
+
+
+def test_tiny_flow_control_windows(golden_cases, sockdir):
+    """A peer that grants the list a thousand bytes at a time (SETTINGS_INITIAL_WINDOW_SIZE =
+    1000, then WINDOW_UPDATEs on the stream; the connection window runs dry too and is topped up):
+    the server never sends a byte more than it was granted, and the pieces add up to the list."""
+    import socket as pysock
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    try:
+        want = table.list_and_watch_bytes()
+        law = b"\x83\x86" + b"\x04" + bytes([len(b"/v1beta1.DevicePlugin/ListAndWatch")]) + \
+            b"/v1beta1.DevicePlugin/ListAndWatch" + _lit(b"content-type", b"application/grpc")
+        s = pysock.socket(pysock.AF_UNIX, pysock.SOCK_STREAM)
+        s.settimeout(5)
+        s.connect(srv.socket)
+        s.sendall(b"PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n" + _frame(4, 0, 0, b"\x00\x04" + (1000).to_bytes(4, "big"))
+                  + _frame(1, 0x04, 1, law) + _frame(0, 0x01, 1, b"\x00\x00\x00\x00\x00"))
+        buf, data, granted_stream, granted_conn = b"", b"", 1000, 65535
+
+        def pump(until):
+            nonlocal buf, data
+            while not until():
+                chunk = s.recv(65536)
+                assert chunk, "server closed early"
+                buf += chunk
+                while len(buf) >= 9 and len(buf) >= 9 + int.from_bytes(buf[:3], "big"):
+                    n = int.from_bytes(buf[:3], "big")
+                    ftype, sid, payload = buf[3], int.from_bytes(buf[5:9], "big"), buf[9:9 + n]
+                    buf = buf[9 + n:]
+                    if ftype == 0 and sid == 1:
+                        data += payload
+        rounds = 0
+        while len(data) < 5 + len(want):
+            pump(lambda: len(data) >= min(granted_stream, granted_conn, 5 + len(want)))
+            assert len(data) <= min(granted_stream, granted_conn), "sent beyond the window"
+            time.sleep(0.02)
+            s.settimeout(0.05)
+            try:
+                extra = s.recv(65536)                      # nothing may arrive while the window is shut
+                buf += extra
+                pump(lambda: True)
+            except (TimeoutError, pysock.timeout):
+                pass
+            s.settimeout(5)
+            assert len(data) <= min(granted_stream, granted_conn)
+            s.sendall(_frame(8, 0, 1, (700).to_bytes(4, "big")))
+            granted_stream += 700
+            rounds += 1
+        assert data[0] == 0 and int.from_bytes(data[1:5], "big") == len(want) and data[5:] == want
+        assert rounds >= 9
+        s.close()
+    finally:
+        srv.Stop()
