@@ -40,6 +40,7 @@ namespace {
 
 constexpr uint64_t kSendSlice = 4u << 20;  // bytes of a device list per turn of the serving loop
 constexpr size_t kMaxStreams = 128;  // advertised in our SETTINGS and enforced
+constexpr size_t kMaxConns = 64;     // kubelet opens one; a bound on descriptors and buffers
 enum Method { kUnknown, kOptions, kListAndWatch, kAllocate, kPreStart, kPreferred };
 const char kServicePrefix[] = "/v1beta1.DevicePlugin/";
 
@@ -861,6 +862,10 @@ void gs_server::accept_one() {
   const int fd = accept4(listen_fd, nullptr, nullptr, SOCK_CLOEXEC);
   if (fd < 0) {
     if (errno == EMFILE || errno == ENFILE || errno == ENOMEM) usleep(10000);  // do not spin on poll
+    return;
+  }
+  if (conns.size() >= kMaxConns) {
+    close(fd);
     return;
   }
   set_io_timeouts(fd, 10);

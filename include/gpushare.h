@@ -303,7 +303,8 @@ GS_API int gs_plugin_stopped(const gs_plugin *p);
  * to the gs_plugin_* entry points above on one serving thread; ListAndWatch
  * sends borrow gs_law_payload's segments, so while a server runs on a table it
  * is that table's one gs_law_payload caller (others use gs_law_encode).
- * Limits: request messages up to max_request_bytes (default 64 MiB; grpc-go's
+ * Limits: 64 connections, 128 open streams on each (advertised and enforced);
+ * request messages up to max_request_bytes (default 64 MiB; grpc-go's
  * default of 4 MiB would refuse a whole B200 at MiB granularity, H12), header
  * blocks up to 256 KiB, Huffman-coded header strings restricted to printable
  * ASCII (see csrc/hpack.h), no message compression (UNIMPLEMENTED, as grpc-go

@@ -620,3 +620,26 @@ def test_tiny_flow_control_windows(golden_cases, sockdir):
         s.close()
     finally:
         srv.Stop()
+
+
+def test_connection_cap(golden_cases, sockdir):
+    """At most 64 connections are held (kubelet opens one): further ones are closed at once,
+    and a slot frees up when a client leaves."""
+    c = _golden(golden_cases)
+    table, plug = product_for_case(c)
+    srv = NativeDevicePluginServer(plug, os.path.join(sockdir, "p.sock"))
+    srv.Start()
+    try:
+        clients = [NativeClient(srv.socket) for _ in range(64)]
+        assert all(cl.call("GetDevicePluginOptions") == b"" for cl in clients)
+        with pytest.raises(L.GpushareError):
+            NativeClient(srv.socket, timeout_ms=500)
+        clients.pop().close()
+        time.sleep(0.3)
+        late = NativeClient(srv.socket)
+        assert late.call("GetDevicePluginOptions") == b""
+        late.close()
+        for cl in clients:
+            cl.close()
+    finally:
+        srv.Stop()
