@@ -180,6 +180,8 @@ SIGNATURES = {
     "gs_probe_inject": (_int, [_vp, _vp, _u64, _u32]),
     "gs_probe_read": (_int, [_vp, _vp, _vp, _u64]),
     "gs_probe_set_variant": (_int, [_vp, _int, _int, _int]),
+    "gs_probe_set_write_rate_auto": (_int, [_vp, _int]),
+    "gs_probe_get_write_rate": (_int, [_vp, _P(_u32), _P(_int)]),
     "gs_probe_set_write_rate": (_int, [_vp, _u32]),
     "gs_probe_verify_noalloc": (_int, [_int, _vp, _P(Slice), _u32, _P(SliceResult)]),
 }

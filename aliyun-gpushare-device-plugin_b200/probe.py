@@ -81,7 +81,17 @@ class Probe:
                 "gs_probe_set_variant")
 
     def set_write_rate(self, gbps):
+        """Fix the store pass's pacing target (0 = unpaced); ends the per-board following."""
         L.check(self.lib.gs_probe_set_write_rate(self.h, gbps), "gs_probe_set_write_rate")
+
+    def set_write_rate_auto(self, on=True):
+        L.check(self.lib.gs_probe_set_write_rate_auto(self.h, int(on)), "gs_probe_set_write_rate_auto")
+
+    def write_rate(self):
+        """-> (current target in GB/s, whether it follows the board)."""
+        g, a = C.c_uint32(), C.c_int()
+        L.check(self.lib.gs_probe_get_write_rate(self.h, C.byref(g), C.byref(a)), "gs_probe_get_write_rate")
+        return g.value, bool(a.value)
 
     @staticmethod
     def _slices(slices):

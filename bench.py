@@ -491,6 +491,7 @@ def run_ours(args, rank, world, local_rank):
                       "bytes_probed": int(la[1]), "bytes_granted": int(la[2]),
                       "coverage": la[1] / la[2] if la[2] else 0, "grants_dropped": int(la[3]),
                       "bad_slices": int(la[6]),
+                      "write_rate_target_gbps_rank0": probe.write_rate()[0],
                       "decisions_per_s_if_every_grant_waited_for_its_sweep":
                           world * TENANTS / ((la[4] + la[5]) / max(la[7], 1) * 1e-3) if live_ms else None,
                       "note": "grants outrun HBM by design: a wave grants ~%d GiB, one sweep of it takes "

@@ -453,8 +453,15 @@ GS_API int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t byt
 GS_API int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
                                 int ctas_per_sm);
 /* Offered rate (GB/s, whole GPU) the store pass paces itself to; 0 = unpaced.
- * Default 7600: B200's write path sustains more when not over-offered.        */
+ * B200's write path sustains more when not over-offered. Default: 7600, fixed.
+ * gs_probe_set_write_rate_auto(p, 1) lets the target back off for a board that
+ * cannot keep up (down 0.8 % after a store pass of >= 4 GiB that fell more than
+ * 1 % behind, back up 0.05 % after one that kept up, never above 7600); off by
+ * default: on healthy boards the fixed target measured better (csrc/probe.cu).
+ * Setting a rate here fixes it and turns the following off.                     */
 GS_API int gs_probe_set_write_rate(gs_probe *p, uint32_t gbps);
+GS_API int gs_probe_set_write_rate_auto(gs_probe *p, int on);
+GS_API int gs_probe_get_write_rate(const gs_probe *p, uint32_t *gbps, int *is_auto);
 /* Read-back pass for callers that may not allocate. No counterpart in the reference
  * (it runs no GPU code). The plugin's health checker on a GPU whose memory is granted
  * to tenants to the last unit cannot cudaMalloc (it would fail, or take what a tenant

@@ -253,3 +253,34 @@ def test_l2_scrub_between_the_passes(probe, oracle_lib):
             probe.run([(d, nbytes, 3)], L.GS_PROBE_SCRUB)          # a scrub alone is not a probe
     finally:
         probe.free(d)
+
+
+def test_write_rate_follows_the_board(probe):
+    """Opt-in following: the pacing target recovers from a start far above the write path's
+    ceiling (where the store pass collapses to ~6.6 TB/s); by default and after an explicit
+    set the target stays where it was put."""
+    nbytes = 16 << 30
+    free, _ = probe.mem_info()
+    if free < nbytes + (2 << 30):
+        pytest.skip("not enough free HBM")
+    d = probe.alloc(nbytes)
+    try:
+        sl = [(d, nbytes, 5)]
+        assert probe.write_rate() == (7600, False)           # the default is fixed
+        probe.set_write_rate(8000)
+        assert probe.write_rate() == (8000, False)
+        _, tm = probe.run(sl, L.GS_PROBE_WRITE)
+        collapsed = nbytes / tm.write_ms / 1e6
+        assert probe.write_rate() == (8000, False)           # explicit: untouched by the pass
+        probe.set_write_rate_auto(True)
+        for _ in range(40):
+            v, tm = probe.run(sl, L.GS_PROBE_WRITE)
+        target, auto = probe.write_rate()
+        settled = nbytes / tm.write_ms / 1e6
+        assert auto and 7000 <= target <= 7600, target
+        assert settled > collapsed + 300 and settled > 7000, (collapsed, settled, target)
+        v, _ = probe.run(sl)
+        assert v[0].clean
+    finally:
+        probe.set_write_rate(7600)                               # the default: fixed
+        probe.free(d)
