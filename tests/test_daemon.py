@@ -62,7 +62,7 @@ def test_daemon_config1_end_to_end(golden_cases, program):
         finally:
             proc.send_signal(signal.SIGTERM)
             try:
-                proc.wait(10)
+                proc.wait(20)
             except subprocess.TimeoutExpired:
                 proc.kill()
             kubelet.stop()
@@ -106,7 +106,7 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, prog
             deadline = time.time() + 15
             while len(kubelet2.registered) == n_before and time.time() < deadline:
                 time.sleep(0.05)
-            assert len(kubelet2.registered) == n_before + 1, "no re-registration after SIGHUP"
+            assert len(kubelet2.registered) >= n_before + 1, "no re-registration after SIGHUP"
             ch = KubeletStub.connect(os.path.join(d, "aliyungpushare.sock"))
             grpc.channel_ready_future(ch).result(timeout=10)
             devs = R.decode_list_and_watch(next(KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")))
@@ -116,7 +116,7 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, prog
         finally:
             proc.send_signal(signal.SIGTERM)
             try:
-                proc.wait(10)
+                proc.wait(20)
             except subprocess.TimeoutExpired:
                 proc.kill()
         assert proc.returncode == 0
@@ -168,7 +168,7 @@ def test_daemon_health_events_reach_the_watch_stream(program):
         finally:
             proc.send_signal(signal.SIGTERM)
             try:
-                proc.wait(10)
+                proc.wait(20)
             except subprocess.TimeoutExpired:
                 proc.kill()
         assert proc.returncode == 0, proc.stderr.read()[-2000:]
