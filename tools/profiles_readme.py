@@ -94,6 +94,12 @@ Both ends of the socket are the library's own HTTP/2 + gRPC transport ("native":
 
 * `r01_bench_launches.md` / `.csv`: ncu launch list of the bench command (store pass ~49.5%%, load pass ~50.5%% of GPU time)
 * `r01_probe_ncu_full.md`: `ncu --set full` of both kernels; DRAM traffic = algorithmic bytes (ratio in `probe_traffic.json`)
+* `r01_write_entropy.txt`: the data written decides the sustained store rate under the 1 kW cap (hashed words 6.6 TB/s,
+  the probe's background+address words 7.2 TB/s, zeros 7.4 TB/s) -- the experiment behind the probe's pattern
+* `r01_rate_sweep_sustained.txt`: sustained store rate against the pacing target (peak 7.56 TB/s at 7 600 GB/s, collapse above);
+  `r01_rate_follow.txt`: the opt-in follower against the fixed target
+* `r01_probe_sizes.json` / `_scrub.json`: rates against slice size, without and with the L2 scrub; `r01_scrub_ncu.md`,
+  `r01_sass_evidence.md`: where a small slice is read back from, and the SASS of the shipped kernels
 """ % (co["config"], co["probe"]["bytes_swept"] / 2**30, min(p["combined_gbps"] for p in pg),
        max(p["combined_gbps"] for p in pg), co["probe"]["aggregate_gbps_wall"] / 1000,
        co["fault_injection"]["victim_tenant"], co["fault_injection"]["flagged_tenants"],
