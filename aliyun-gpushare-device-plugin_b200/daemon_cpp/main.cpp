@@ -60,9 +60,33 @@ void logv(int level, const char *fmt, ...) {
   fflush(stderr);
 }
 
+// flag.PrintDefaults of the ten reference flags (main.go:15-26) and the additions
+void print_usage() {
+  fputs("Usage of gpushare-device-plugin-v2:\n"
+        "  -client-cert string\n    \tKubelet TLS client certificate\n"
+        "  -client-key string\n    \tKubelet TLS client key\n"
+        "  -health-check\n    \tEnable or disable Health check\n"
+        "  -kubelet-address string\n    \tKubelet IP Address (default \"0.0.0.0\")\n"
+        "  -kubelet-port uint\n    \tKubelet listened Port (default 10250)\n"
+        "  -memory-unit string\n    \tSet memoryUnit of the GPU Memroy, support 'GiB' and 'MiB' (default \"GiB\")\n"
+        "  -mps\n    \tEnable or Disable MPS\n"
+        "  -query-kubelet\n    \tQuery pending pods from kubelet instead of kube-apiserver\n"
+        "  -timeout int\n    \tKubelet client http timeout duration (default 10)\n"
+        "  -token string\n    \tKubelet client bearer token\n"
+        "  -logtostderr, -v int\n    \tglog flags the DaemonSet passes; -v sets the verbosity\n"
+        "additions:\n"
+        "  -health-probe-interval int\n    \twith -probe and -health-check: every N seconds sweep each GPU's free memory (0 = off)\n"
+        "  -no-register\n    \tserve without registering with kubelet\n"
+        "  -nvml-lib string\n    \tpath of libnvidia-ml\n"
+        "  -pod-source-file string\n    \tJSON file with the node's pods (stands in for the lister)\n"
+        "  -probe\n    \tsweep each granted slice on the GPU after Allocate\n"
+        "  -socket-dir string\n    \tdevice-plugins directory (default \"/var/lib/kubelet/device-plugins\")\n",
+        stderr);
+}
+
 [[noreturn]] void usage_error(const std::string &msg) {
-  fprintf(stderr, "%s\nUsage of gpushare-device-plugin-v2: see cmd/nvidia/main.go:15-26 for the flags\n",
-          msg.c_str());
+  fprintf(stderr, "%s\n", msg.c_str());
+  print_usage();
   exit(2);  // Go's flag.ExitOnError
 }
 
@@ -89,6 +113,10 @@ Flags parse_flags(int argc, char **argv) {
     if (a.size() < 2 || a[0] != '-') break;  // first non-flag argument ends parsing
     if (a == "--") break;
     a = a.substr(a[1] == '-' ? 2 : 1);
+    if (a == "h" || a == "help") {  // flag.ErrHelp: usage, exit status 0
+      print_usage();
+      exit(0);
+    }
     std::string val;
     bool has_val = false;
     const size_t eq = a.find('=');
