@@ -28,7 +28,7 @@ all: $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON) $(INSPECT) $(PODGETTER)
 $(CSRC)/%.o: $(CSRC)/%.cpp include/gpushare.h $(wildcard $(CSRC)/*.h)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
 
-$(CSRC)/%.o: $(CSRC)/%.cu include/gpushare.h $(wildcard $(CSRC)/*.h)
+$(CSRC)/%.o: $(CSRC)/%.cu include/gpushare.h $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh)
 	$(NVCC) $(NVCCFLAGS) -c $< -o $@
 
 $(CORE_SO): $(OBJS)

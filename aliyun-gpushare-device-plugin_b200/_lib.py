@@ -17,6 +17,7 @@ GS_ALL_GPUS = -1
 GS_UUID_MAX = 96
 GS_PROBE_MAX_SLICES = 64
 GS_PROBE_WRITE, GS_PROBE_VERIFY, GS_PROBE_SCRUB = 1, 2, 4
+GS_PROBE_PATTERN_LOWTOGGLE, GS_PROBE_PATTERN_HASH = 0, 1
 (GS_ALLOC_MATCHED, GS_ALLOC_SINGLE_GPU, GS_ALLOC_ERR_NO_MATCH, GS_ALLOC_ERR_BAD_INDEX,
  GS_ALLOC_ERR_PODS, GS_ALLOC_ERR_PATCH) = range(6)
 
@@ -58,7 +59,7 @@ class AllocResult(C.Structure):
 
 class Slice(C.Structure):
     _fields_ = [("base", C.c_void_p), ("bytes", C.c_uint64), ("seed", C.c_uint32),
-                ("tag", C.c_uint32)]
+                ("tag", C.c_uint32), ("pattern", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class SliceResult(C.Structure):

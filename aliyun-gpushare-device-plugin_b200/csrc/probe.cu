@@ -1,20 +1,7 @@
-// probe.cu -- K1, the HBM slice probe (sm_100a). No counterpart in the reference:
-// cjg/aliyun-gpushare-device-plugin runs no GPU code.
-//
-// A batch of up to GS_PROBE_MAX_SLICES granted ranges is probed by two launches:
-//   probe_write_bulk_kernel (default) : pattern(i, seed) -> shared memory (128-bit
-//                        STS), then cp.async.bulk (TMA engine) full-line stores
-//   probe_write_kernel : buf[i] = pattern(i, seed)       128-bit coalesced STG
-//                        (selectable; tops out ~15% lower)
-//   probe_verify_kernel: buf[i] == pattern(i, seed) ?    128-bit coalesced loads,
-//                        warp-ballot reduction, atomics only on the error path
-// Work is cut into 64 KiB tiles laid end to end over all slices of the batch; a
-// persistent grid (SMs x resident CTAs) strides over the tiles, so one launch
-// serves one 40 GiB slice or 64 small tenants equally well. Slice descriptors
-// travel as kernel parameters (no host->device copy); the only device memory
-// beyond the probed ranges is the per-slice result table.
-//
-// Algorithmic traffic: 1 byte stored + 1 byte loaded per slice byte.
+// probe.cu -- host side of K1, the HBM slice probe (sm_100a): engines, variant dispatch,
+// launches and the extern "C" entry points. The kernels are in probe_kernels.cuh. No
+// counterpart in the reference: cjg/aliyun-gpushare-device-plugin runs no GPU code
+// (SURVEY.md section 8, row K1).
 
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -26,391 +13,11 @@
 
 #include "gpushare.h"
 #include "internal.h"
+#include "probe_kernels.cuh"
 
 namespace {
 
-constexpr int kThreads = 256;
-constexpr uint32_t kTileVec = 4096;  // 16-byte words per tile = 64 KiB
-
-struct SliceDesc {
-  uint4 *base;
-  uint64_t n_vec;       // 16-byte words in the slice
-  uint64_t tile_begin;  // first tile of this slice in the batch's tile space
-  uint64_t tile_end;    // one past its last tile
-  uint32_t seed;
-  uint32_t pad;
-};
-
-struct Batch {
-  SliceDesc s[GS_PROBE_MAX_SLICES];
-  uint64_t total_tiles;
-  uint32_t n;
-  uint32_t pad;
-};
-
-// Device-side result row; converted to gs_slice_result on the host.
-struct DevResult {
-  unsigned long long mismatches;
-  unsigned long long inv_first_bad;  // max over ~byte_offset; 0 = none (memset-able)
-  unsigned long long bit_flips;
-  unsigned long long reserved;
-};
-
-// pattern(i, seed): i = index of the 16-byte word inside the slice.
-//
-//   background(seed) = four 32-bit words r0..r3 drawn once per sweep from the seed
-//   word(i)          = { r0 ^ lo(i), r1 ^ hi(i), r2, r3 }
-//
-// Every cell holds a pseudo-random bit that changes with the seed (both polarities over
-// successive sweeps; a stale sweep never matches), and every 16-byte word carries its own
-// address, so aliased, shifted, dropped or zeroed words all mismatch. What the pattern
-// deliberately does NOT do is change many bits from one word to the next: under the board's
-// power cap the store pass is priced by how many bits toggle between the transfers that
-// different SMs interleave on the shared path to HBM. A per-word avalanche hash (the first
-// version of this pattern) sustains 6.6 TB/s of stores; this form, which toggles ~8 bits per
-// 128, sustains 7.2 TB/s (tools/exp/write_entropy9.cu, profiles/r01_write_entropy.txt).
-// Restated on the CPU in oracle/pattern.c (test infrastructure only).
-struct Background {
-  uint32_t r0, r1, r2, r3;
-};
-__device__ __forceinline__ Background slice_background(uint32_t seed) {
-  uint32_t r = seed * 0x9E3779B1u + 0x7F4A7C15u;
-  r ^= r >> 15;
-  r *= 0x2C1B3C6Du;
-  r ^= r >> 12;
-  Background b;
-  b.r0 = r;
-  b.r1 = b.r0 * 0x85EBCA77u + 1u;
-  b.r2 = b.r1 * 0xC2B2AE3Du + 1u;
-  b.r3 = b.r2 * 0x27D4EB2Fu + 1u;
-  return b;
-}
-__device__ __forceinline__ uint4 slice_pattern(uint64_t i, uint32_t seed) {
-  const Background b = slice_background(seed);
-  return make_uint4(b.r0 ^ (uint32_t)i, b.r1 ^ (uint32_t)(i >> 32), b.r2, b.r3);
-}
-
-// The same function, split for the kernels' inner loops: a tile is 4096 words and starts on
-// a multiple of 4096, so the background and the high index word are folded once per tile and
-// one add and one xor per word remain. Bit-identical to slice_pattern.
-struct TilePattern {
-  uint32_t r0, y, z, w;  // y = r1 ^ hi; z, w = r2, r3
-  uint32_t lo0;          // low index word of the tile's first word
-  __device__ __forceinline__ TilePattern(uint64_t v0, uint32_t seed) {
-    const Background b = slice_background(seed);
-    r0 = b.r0;
-    y = b.r1 ^ (uint32_t)(v0 >> 32);
-    z = b.r2;
-    w = b.r3;
-    lo0 = (uint32_t)v0;
-  }
-  __device__ __forceinline__ uint4 word(uint32_t j) const {  // j < kTileVec
-    return make_uint4(r0 ^ (lo0 + j), y, z, w);
-  }
-};
-
-// ---- 128-bit global accesses, one PTX form per variant ----------------------
-template <int V>
-__device__ __forceinline__ void st128(uint4 *p, const uint4 &v, uint64_t policy) {
-  if constexpr (V == 1) {
-    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x),
-                 "r"(v.y), "r"(v.z), "r"(v.w)
-                 : "memory");
-  } else if constexpr (V == 2) {
-    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p),
-                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
-                 : "memory");
-  } else if constexpr (V == 3) {
-    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p),
-                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(policy)
-                 : "memory");
-  } else {
-    asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x),
-                 "r"(v.y), "r"(v.z), "r"(v.w)
-                 : "memory");
-  }
-}
-
-template <int V>
-__device__ __forceinline__ uint4 ld128(const uint4 *p, uint64_t policy) {
-  uint4 r;
-  if constexpr (V == 1) {
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-  } else if constexpr (V == 2) {
-    asm volatile("ld.global.cs.v4.u32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-  } else if constexpr (V == 3) {
-    asm volatile(
-        "ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
-        : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-        : "l"(p), "l"(policy));
-  } else if constexpr (V == 4) {
-    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.u32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-  } else {
-    asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-  }
-  return r;
-}
-
-__device__ __forceinline__ uint64_t evict_first_policy() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-
-// ---- store pass --------------------------------------------------------------
-template <int U, int V>
-__global__ void __launch_bounds__(kThreads)
-    probe_write_kernel(const __grid_constant__ Batch b) {
-  uint64_t policy = 0;
-  if constexpr (V == 3) policy = evict_first_policy();
-  uint32_t cur = 0;
-  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
-    while (tile >= b.s[cur].tile_end) ++cur;
-    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
-    const uint64_t rem = b.s[cur].n_vec - v0;
-    const TilePattern pat(v0, b.s[cur].seed);
-    uint4 *p = b.s[cur].base + v0;
-    if (rem >= kTileVec) {
-#pragma unroll 1
-      for (uint32_t k = 0; k < kTileVec; k += kThreads * U) {
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t j = k + u * kThreads + threadIdx.x;
-          st128<V>(p + j, pat.word(j), policy);
-        }
-      }
-    } else {
-      for (uint32_t j = threadIdx.x; j < (uint32_t)rem; j += kThreads)
-        st128<V>(p + j, pat.word(j), policy);
-    }
-  }
-}
-
-// ---- store pass through the TMA engine ----------------------------------------
-// Plain STG.128 stores plateau near 6.3 TB/s on B200; the same bytes sent as bulk
-// asynchronous shared->global copies reach the rate the copy engine's memset gets
-// (7.4 TB/s). One CTA per SM owns a ring of STAGES 64 KiB tiles in shared memory:
-// all threads fill a tile with the pattern (conflict-free 128-bit STS), then the
-// first kTileVec/sub_vec threads each issue one bulk store of sub_vec words.
-//
-// Pacing. B200's write path degrades when it is offered more than it can drain:
-// unpaced, this kernel (like plain STG) settles near 6.4 TB/s, while the same
-// stores offered at just under the drain rate sustain 7.3+ TB/s (measured; see
-// DESIGN.md "write pacing"). So each CTA runs a token bucket on %globaltimer
-// (32 ns steps on B200): one tile per period_x16/16 ns, never bursting to catch
-// up. period_x16 == 0 disables pacing.
-__device__ __forceinline__ uint64_t global_timer_ns() {
-  uint64_t t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-template <int STAGES, int THREADS, bool HINT = false>
-__global__ void __launch_bounds__(THREADS, 1)
-    probe_write_bulk_kernel(const __grid_constant__ Batch b, uint32_t sub_vec,
-                            uint32_t period_x16) {
-  extern __shared__ __align__(128) uint4 ring[];
-  uint64_t policy = 0;
-  if constexpr (HINT) policy = evict_first_policy();
-  const uint32_t nsub = kTileVec / sub_vec;
-  uint32_t cur = 0;
-  int stage = 0;
-  // the bucket's clock is time since kernel start, in 1/16 ns, so it cannot wrap
-  const uint64_t t_start = period_x16 ? global_timer_ns() : 0;
-  uint64_t next_x16 = 0;
-  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
-    while (tile >= b.s[cur].tile_end) ++cur;
-    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
-    const uint64_t rem64 = b.s[cur].n_vec - v0;
-    const uint32_t rem = rem64 >= kTileVec ? kTileVec : (uint32_t)rem64;
-    const TilePattern pat(v0, b.s[cur].seed);
-    uint4 *buf = ring + (size_t)stage * kTileVec;
-    // the bulk store that last read this stage must have drained shared memory
-    if (threadIdx.x < nsub)
-      asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(STAGES - 1) : "memory");
-    __syncthreads();
-    if (rem == kTileVec) {
-#pragma unroll 4
-      for (uint32_t j = threadIdx.x; j < kTileVec; j += THREADS)
-        buf[j] = pat.word(j);
-    } else {
-      for (uint32_t j = threadIdx.x; j < rem; j += THREADS) buf[j] = pat.word(j);
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();
-    if (threadIdx.x < nsub) {
-      if (period_x16) {
-        uint64_t now;
-        while ((now = (global_timer_ns() - t_start) * 16) < next_x16) {
-          __nanosleep(32);  // park the warp instead of burning issue slots (the board is power-capped)
-        }
-        if (now > next_x16 + period_x16) next_x16 = now;  // late: do not burst
-        next_x16 += period_x16;
-      }
-      const uint32_t first = threadIdx.x * sub_vec;
-      if (first < rem) {
-        const uint32_t cnt = rem - first < sub_vec ? rem - first : sub_vec;
-        const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf + first);
-        if constexpr (HINT)
-          asm volatile(
-              "cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(
-                  b.s[cur].base + v0 + first),
-              "r"(saddr), "r"(cnt * 16u), "l"(policy)
-              : "memory");
-        else
-          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
-                           b.s[cur].base + v0 + first),
-                       "r"(saddr), "r"(cnt * 16u)
-                       : "memory");
-      }
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    }
-    stage = stage + 1 == STAGES ? 0 : stage + 1;
-  }
-  if (threadIdx.x < nsub) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-// ---- paced plain stores --------------------------------------------------------------
-// The same token bucket applied to ordinary STG.128 stores (one CTA per SM, `sub_vec` words
-// per token): pacing, not the TMA engine, is what lifts the store pass off the 6.3 TB/s
-// plateau (tools/exp/stg_paced8.cu: 7.2-7.45 TB/s at 16 KiB per token). No shared memory.
-__global__ void __launch_bounds__(kThreads)
-    probe_write_paced_kernel(const __grid_constant__ Batch b, uint32_t sub_vec, uint32_t period_x16) {
-  uint32_t cur = 0;
-  const uint64_t t_start = period_x16 ? global_timer_ns() : 0;
-  // spread the CTAs' first tokens over one period so they do not all fire together
-  uint64_t next_x16 = (uint64_t)period_x16 * blockIdx.x / gridDim.x;
-  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
-    while (tile >= b.s[cur].tile_end) ++cur;
-    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
-    const uint64_t rem64 = b.s[cur].n_vec - v0;
-    const uint32_t rem = rem64 >= kTileVec ? kTileVec : (uint32_t)rem64;
-    const TilePattern pat(v0, b.s[cur].seed);
-    uint4 *p = b.s[cur].base + v0;
-    for (uint32_t s0 = 0; s0 < rem; s0 += sub_vec) {
-      if (period_x16 && threadIdx.x < 32) {
-        uint64_t now;
-        while ((now = (global_timer_ns() - t_start) * 16) < next_x16) {
-          __nanosleep(32);  // park the warp instead of burning issue slots (the board is power-capped)
-        }
-        if (now > next_x16 + period_x16) next_x16 = now;  // late: do not burst
-        next_x16 += period_x16;
-      }
-      __syncthreads();  // the other warps sleep here until warp 0 holds the token
-      const uint32_t s1 = s0 + sub_vec < rem ? s0 + sub_vec : rem;
-#pragma unroll 4
-      for (uint32_t j = s0 + threadIdx.x; j < s1; j += kThreads) st128<0>(p + j, pat.word(j), 0);
-    }
-  }
-}
-
-// ---- load + compare pass -----------------------------------------------------
-__device__ __forceinline__ bool differs(const uint4 &a, const uint4 &b) {
-  return ((a.x ^ b.x) | (a.y ^ b.y) | (a.z ^ b.z) | (a.w ^ b.w)) != 0u;
-}
-
-// Error path: every lane of the warp calls this with its own verdict. One lane
-// (the one holding the lowest bad address) issues the atomics for the warp.
-__device__ __noinline__ void report_warp(DevResult *res, bool bad, uint4 got, uint4 want,
-                                         uint64_t vec_index) {
-  const unsigned m = __ballot_sync(0xffffffffu, bad);
-  if (m == 0u) return;
-  unsigned flips = 0;
-  if (bad)
-    flips = __popc(got.x ^ want.x) + __popc(got.y ^ want.y) + __popc(got.z ^ want.z) +
-            __popc(got.w ^ want.w);
-  flips = __reduce_add_sync(0xffffffffu, flips);
-  const unsigned leader = __ffs(m) - 1;
-  if ((threadIdx.x & 31u) == leader) {
-    uint32_t d = got.x ^ want.x, word = 0;
-    if (d == 0u) { d = got.y ^ want.y; word = 1; }
-    if (d == 0u) { d = got.z ^ want.z; word = 2; }
-    if (d == 0u) { d = got.w ^ want.w; word = 3; }
-    const uint64_t byte_off = vec_index * 16ull + word * 4u + ((__ffs(d) - 1) >> 3);
-    atomicAdd(&res->mismatches, (unsigned long long)__popc(m));
-    atomicAdd(&res->bit_flips, (unsigned long long)flips);
-    atomicMax(&res->inv_first_bad, ~(unsigned long long)byte_off);
-  }
-}
-
-template <int U, int V>
-__global__ void __launch_bounds__(kThreads)
-    probe_verify_kernel(const __grid_constant__ Batch b, DevResult *__restrict__ results) {
-  uint64_t policy = 0;
-  if constexpr (V == 3) policy = evict_first_policy();
-  uint32_t cur = 0;
-  for (uint64_t tile = blockIdx.x; tile < b.total_tiles; tile += gridDim.x) {
-    while (tile >= b.s[cur].tile_end) ++cur;
-    const uint64_t v0 = (tile - b.s[cur].tile_begin) * kTileVec;
-    const uint64_t rem = b.s[cur].n_vec - v0;
-    const TilePattern pat(v0, b.s[cur].seed);
-    const uint4 *p = b.s[cur].base + v0;
-    if (rem >= kTileVec) {
-#pragma unroll 1
-      for (uint32_t k = 0; k < kTileVec; k += kThreads * U) {
-        uint4 got[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u)  // all loads in flight before any compare
-          got[u] = ld128<V>(p + k + u * kThreads + threadIdx.x, policy);
-        bool any = false;
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t j = k + u * kThreads + threadIdx.x;
-          any |= differs(got[u], pat.word(j));
-        }
-        if (__any_sync(0xffffffffu, any)) {
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const uint32_t j = k + u * kThreads + threadIdx.x;
-            const uint4 want = pat.word(j);
-            report_warp(results + cur, differs(got[u], want), got[u], want, v0 + j);
-          }
-        }
-      }
-    } else {
-      // ragged last tile of a slice: bounds as a predicate so the warp stays whole
-      const uint32_t r = (uint32_t)rem;
-      for (uint32_t k = 0; k < r; k += kThreads) {
-        const uint32_t j = k + threadIdx.x;
-        const bool inb = j < r;
-        const uint4 want = pat.word(j);
-        const uint4 got = inb ? ld128<V>(p + j, policy) : want;
-        const bool bad = differs(got, want);
-        if (__any_sync(0xffffffffu, bad)) report_warp(results + cur, bad, got, want, v0 + j);
-      }
-    }
-  }
-}
-
-__global__ void probe_inject_kernel(uint32_t *word, uint32_t mask) { *word ^= mask; }
-
-// ---- L2 scrub ------------------------------------------------------------------------
-// Between the passes (GS_PROBE_SCRUB): stream a buffer larger than the L2 through it, so the
-// store pass's dirty lines are written back and the slice's lines are displaced. The load
-// pass then comes from DRAM even when the slice is smaller than the L2, and no longer has
-// the write-back running underneath it.
-constexpr uint64_t kScrubBytes = 192ull << 20;  // L2 is 126 MB
-__global__ void __launch_bounds__(kThreads)
-    probe_scrub_kernel(uint4 *__restrict__ buf, uint64_t n_vec, uint32_t mode) {
-  const uint64_t stride = (uint64_t)gridDim.x * kThreads;
-  uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
-  if (mode == 0) {
-    // stores also displace the slice, but leave 192 MiB of dirty lines behind for the load pass
-    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    for (; i < n_vec; i += stride) st128<0>(buf + i, z, 0);
-  } else {
-    uint32_t acc = 0;
-    for (; i < n_vec; i += stride) acc ^= ld128<0>(buf + i, 0).x;
-    if (acc == 0x9E3779B9u) buf[0].x = acc;  // zero-filled buffer: never taken, keeps the loads
-  }
-}
+using namespace gs_probe_dev;
 
 // ---- variant dispatch ----------------------------------------------------------
 using WriteFn = void (*)(const Batch);
@@ -439,6 +46,32 @@ bool is_bulk_code(int code) {
 }
 constexpr int kNumVerifyVariants = 5;
 constexpr int kNumUnrolls = 3;  // U = 2, 4, 8 -> variant index / 10 selects
+// Bulk-load verify codes: 500 + 100 * hint + 10 * chunk_sel + warps_sel
+//   hint      0 -> plain bulk loads, 1 -> with an L2 evict-first hint (codes 600..)
+//   chunk_sel 0 -> 16 KiB stages, 1 -> 32 KiB, 2 -> 64 KiB (the ring holds as many as fit)
+//   warps_sel 0 -> 4 consumer warps, 1 -> 8, 2 -> 16 (plus the producer warp)
+constexpr int kVerifyBulkBase = 500;
+constexpr uint32_t kVerifyBulkRingBytes = 192u << 10;  // per SM; split between the CTAs of an SM
+bool is_bulk_verify_code(int code) {
+  return code >= kVerifyBulkBase && code < kVerifyBulkBase + 200 && (code % 100) / 10 < 3 &&
+         code % 10 < 3;
+}
+using VerifyBulkFn = void (*)(const Batch, DevResult *, uint32_t);
+template <bool HINT>
+VerifyBulkFn verify_bulk_fn_h(int chunk_sel, int warps_sel) {
+  static const VerifyBulkFn fns[3][3] = {
+      {probe_verify_bulk_kernel<1024, 4, HINT>, probe_verify_bulk_kernel<1024, 8, HINT>,
+       probe_verify_bulk_kernel<1024, 16, HINT>},
+      {probe_verify_bulk_kernel<2048, 4, HINT>, probe_verify_bulk_kernel<2048, 8, HINT>,
+       probe_verify_bulk_kernel<2048, 16, HINT>},
+      {probe_verify_bulk_kernel<4096, 4, HINT>, probe_verify_bulk_kernel<4096, 8, HINT>,
+       probe_verify_bulk_kernel<4096, 16, HINT>}};
+  return fns[chunk_sel][warps_sel];
+}
+VerifyBulkFn verify_bulk_fn(int code) {
+  const int c = (code % 100) / 10, w = code % 10;
+  return code >= kVerifyBulkBase + 100 ? verify_bulk_fn_h<true>(c, w) : verify_bulk_fn_h<false>(c, w);
+}
 
 template <int U>
 WriteFn write_fn_u(int v) {
@@ -506,6 +139,7 @@ struct gs_probe {
   bool pending = false;
   int write_variant = kDefaultWriteVariant;
   bool bulk_attr_set[9] = {false, false, false, false, false, false, false, false, false};
+  bool verify_bulk_attr_set[18] = {};
   uint32_t write_rate_gbps = kDefaultWriteRateGBps;  // 0 = unpaced
   bool write_rate_auto = false;  // opt-in: back off for a board that cannot keep up (tune_write_rate)
   int verify_variant = 10;  // U = 2, plain ld.global.v4: 30 registers, 8 CTAs/SM resident;
@@ -518,6 +152,7 @@ struct gs_probe {
     cudaError_t e_ = (call);                               \
     if (e_ != cudaSuccess) {                               \
       gs_internal::set_cuda_error(#call, (int)e_, cudaGetErrorString(e_)); \
+      (void)cudaGetLastError(); /* read it off, or the next launch check reports it again */ \
       return GS_E_CUDA;                                    \
     }                                                      \
   } while (0)
@@ -536,7 +171,10 @@ int gs_probe_open(int cuda_ordinal, gs_probe **out) {
     return GS_E_CUDA;
   }
   gs_probe *p = new (std::nothrow) gs_probe();
-  if (!p) return GS_E_INVAL;
+  if (!p) {
+    gs_internal::set_cuda_error("gs_probe_open", 0, "out of host memory");
+    return GS_E_CUDA;
+  }
   p->dev = cuda_ordinal;
   if (const char *m = getenv("GS_PROBE_SCRUB_MODE")) p->scrub_mode = (uint32_t)atoi(m);
   cudaError_t e = cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, cuda_ordinal);
@@ -546,6 +184,7 @@ int gs_probe_open(int cuda_ordinal, gs_probe **out) {
   if (e == cudaSuccess) e = cudaMallocHost(&p->h_res, sizeof(DevResult) * GS_PROBE_MAX_SLICES);
   if (e != cudaSuccess) {
     gs_internal::set_cuda_error("gs_probe_open", (int)e, cudaGetErrorString(e));
+    (void)cudaGetLastError();
     gs_probe_close(p);
     return GS_E_CUDA;
   }
@@ -607,7 +246,8 @@ int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
     p->write_variant = write_variant;
   }
   if (verify_variant >= 0) {
-    if (!valid_code(verify_variant, kNumVerifyVariants)) return GS_E_INVAL;
+    if (!valid_code(verify_variant, kNumVerifyVariants) && !is_bulk_verify_code(verify_variant))
+      return GS_E_INVAL;
     p->verify_variant = verify_variant;
   }
   if (ctas_per_sm >= 0) {
@@ -671,6 +311,32 @@ static int grid_for(const gs_probe *p, const void *fn, uint64_t total_tiles, int
   return GS_OK;
 }
 
+// Slice list -> tile space. Returns GS_E_INVAL for a slice that is not a 16-byte aligned,
+// non-empty multiple of 16 bytes or names an unknown pattern.
+static int build_batch(const gs_slice *slices, uint32_t n, Batch *b, uint64_t *bytes_out) {
+  memset(b, 0, sizeof(*b));
+  uint64_t tiles = 0, bytes = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const gs_slice &s = slices[i];
+    if (!s.base || s.bytes == 0 || (s.bytes & 15u) || ((uintptr_t)s.base & 15u)) return GS_E_INVAL;
+    if (s.pattern != GS_PROBE_PATTERN_LOWTOGGLE && s.pattern != GS_PROBE_PATTERN_HASH)
+      return GS_E_INVAL;
+    SliceDesc &d = b->s[i];
+    d.base = (uint4 *)s.base;
+    d.n_vec = s.bytes / 16;
+    d.tile_begin = tiles;
+    tiles += (d.n_vec + kTileVec - 1) / kTileVec;
+    d.tile_end = tiles;
+    d.seed = s.seed;
+    d.pattern = s.pattern;
+    bytes += s.bytes;
+  }
+  b->total_tiles = tiles;
+  b->n = n;
+  if (bytes_out) *bytes_out = bytes;
+  return GS_OK;
+}
+
 int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t passes) {
   if (!p || !slices || n == 0 || (passes & ~(GS_PROBE_WRITE | GS_PROBE_VERIFY | GS_PROBE_SCRUB)) ||
       (passes & (GS_PROBE_WRITE | GS_PROBE_VERIFY)) == 0)
@@ -678,24 +344,16 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
   if (n > GS_PROBE_MAX_SLICES) return GS_E_LIMIT;
   if (p->pending) return GS_E_STATE;
   Batch b;
-  memset(&b, 0, sizeof(b));
-  uint64_t tiles = 0, bytes = 0;
-  for (uint32_t i = 0; i < n; ++i) {
-    const gs_slice &s = slices[i];
-    if (!s.base || s.bytes == 0 || (s.bytes & 15u) || ((uintptr_t)s.base & 15u)) return GS_E_INVAL;
-    SliceDesc &d = b.s[i];
-    d.base = (uint4 *)s.base;
-    d.n_vec = s.bytes / 16;
-    d.tile_begin = tiles;
-    tiles += (d.n_vec + kTileVec - 1) / kTileVec;
-    d.tile_end = tiles;
-    d.seed = s.seed;
-    bytes += s.bytes;
-  }
-  b.total_tiles = tiles;
-  b.n = n;
+  uint64_t bytes = 0;
+  if (int rc = build_batch(slices, n, &b, &bytes)) return rc;
+  const uint64_t tiles = b.total_tiles;
 
   DeviceGuard g(p->dev);
+  if (!g.ok) {
+    gs_internal::set_cuda_error("cudaSetDevice", -1, "cannot select device");
+    return GS_E_CUDA;
+  }
+  (void)cudaGetLastError();  // an error some earlier call on this thread left unread is not ours
   uint32_t launches = 0;
   GS_CUDA(cudaMemsetAsync(p->d_res, 0, sizeof(DevResult) * n, p->stream));
   GS_CUDA(cudaEventRecord(p->ev[0], p->stream));
@@ -760,7 +418,28 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
     ++launches;
   }
   GS_CUDA(cudaEventRecord(p->ev[4], p->stream));
-  if (passes & GS_PROBE_VERIFY) {
+  if ((passes & GS_PROBE_VERIFY) && is_bulk_verify_code(p->verify_variant)) {
+    const int code = p->verify_variant;
+    const int chunk_sel = (code % 100) / 10, warps_sel = code % 10;
+    const uint32_t chunk_bytes = 16384u << chunk_sel;
+    const int per_sm = p->ctas_per_sm == 2 ? 2 : 1;  // the ring is an SM's shared memory, split
+    uint32_t stages = kVerifyBulkRingBytes / (uint32_t)per_sm / chunk_bytes;
+    if (stages > kBulkMaxStages) stages = kBulkMaxStages;
+    const size_t smem = (size_t)stages * chunk_bytes;
+    VerifyBulkFn fn = verify_bulk_fn(code);
+    // the attribute is a maximum: set it once per kernel to the whole ring
+    const int slot = (code >= kVerifyBulkBase + 100 ? 9 : 0) + chunk_sel * 3 + warps_sel;
+    if (!p->verify_bulk_attr_set[slot]) {
+      GS_CUDA(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)kVerifyBulkRingBytes));
+      p->verify_bulk_attr_set[slot] = true;
+    }
+    uint64_t grid = (uint64_t)p->sms * (uint64_t)per_sm;
+    if (grid > tiles) grid = tiles;
+    fn<<<(int)grid, 32 + 32 * (4 << warps_sel), smem, p->stream>>>(b, p->d_res, stages);
+    GS_CUDA(cudaGetLastError());
+    ++launches;
+  } else if (passes & GS_PROBE_VERIFY) {
     VerifyFn fn = verify_fn(p->verify_variant);
     int grid = 0;
     int rc = grid_for(p, (const void *)fn, tiles, &grid);
@@ -905,21 +584,8 @@ extern "C" int gs_probe_verify_noalloc(int cuda_ordinal, void *stream, const gs_
     return GS_E_LIMIT;
   }
   Batch b;
-  memset(&b, 0, sizeof(b));
-  uint64_t tiles = 0;
-  for (uint32_t i = 0; i < n; ++i) {
-    const gs_slice &s = slices[i];
-    if (!s.base || s.bytes == 0 || (s.bytes & 15u) || ((uintptr_t)s.base & 15u)) return GS_E_INVAL;
-    SliceDesc &d = b.s[i];
-    d.base = (uint4 *)s.base;
-    d.n_vec = s.bytes / 16;
-    d.tile_begin = tiles;
-    tiles += (d.n_vec + kTileVec - 1) / kTileVec;
-    d.tile_end = tiles;
-    d.seed = s.seed;
-  }
-  b.total_tiles = tiles;
-  b.n = n;
+  if (int rc = build_batch(slices, n, &b, nullptr)) return rc;
+  const uint64_t tiles = b.total_tiles;
 
   DeviceGuard g(cuda_ordinal);
   if (!g.ok) {
@@ -943,6 +609,7 @@ extern "C" int gs_probe_verify_noalloc(int cuda_ordinal, void *stream, const gs_
     sms = g_noalloc_sms[cuda_ordinal];
   }
   cudaStream_t st = (cudaStream_t)stream;
+  (void)cudaGetLastError();  // an error some earlier call on this thread left unread is not ours
   // the table still holds the previous call's verdicts: the rows this call uses start at zero
   GS_CUDA(cudaMemsetAsync(table, 0, sizeof(DevResult) * n, st));
   uint64_t grid = (uint64_t)sms * 8u;

@@ -96,9 +96,10 @@ class Probe:
     @staticmethod
     def _slices(slices):
         arr = (L.Slice * len(slices))()
-        for i, s in enumerate(slices):
+        for i, s in enumerate(slices):      # (base, bytes, seed[, tag[, pattern]])
             base, nbytes, seed = s[0], s[1], s[2]
-            arr[i] = L.Slice(base, nbytes, seed, s[3] if len(s) > 3 else i)
+            arr[i] = L.Slice(base, nbytes, seed, s[3] if len(s) > 3 else i,
+                             s[4] if len(s) > 4 else L.GS_PROBE_PATTERN_LOWTOGGLE, 0)
         return arr
 
     def submit(self, slices, passes=L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY):

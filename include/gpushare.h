@@ -384,11 +384,24 @@ GS_API const char *gs_grpc_last_error(void); /* thread-local, valid until the ne
  * errors with a warp ballot. Two passes => 2 algorithmic bytes per slice byte. */
 typedef struct gs_probe gs_probe;
 
+/* pattern(i, seed) written to and expected in the slice's i-th 16-byte word.
+ *   LOWTOGGLE  { r0 ^ lo(i), r1 ^ hi(i), r2, r3 }, r0..r3 drawn from the seed once per sweep:
+ *              every cell gets a seed-dependent bit and every word its own address, while
+ *              few bits change from word to word -- which is what the power-capped store
+ *              pass is priced by. The fast form; what grants are swept with.
+ *   HASH       { h, ~h, h * K + lo(i), rotl(h, 13) ^ hi(i) ^ C }, h an avalanche hash of
+ *              (i, seed): every lane carries the address, both polarities in one sweep. The
+ *              strong form; what health-time sweeps use. Costs ~9 % of the store rate.  */
+#define GS_PROBE_PATTERN_LOWTOGGLE 0
+#define GS_PROBE_PATTERN_HASH 1
+
 typedef struct gs_slice {
   void *base;        /* device pointer, 16-byte aligned                        */
   uint64_t bytes;    /* multiple of 16                                         */
-  uint32_t seed;
+  uint32_t seed;     /* change it every sweep: a stale sweep then never matches */
   uint32_t tag;      /* caller cookie (e.g. pod index); not interpreted        */
+  uint32_t pattern;  /* GS_PROBE_PATTERN_*; anything else => GS_E_INVAL        */
+  uint32_t reserved; /* 0                                                      */
 } gs_slice;
 
 typedef struct gs_slice_result {
@@ -449,7 +462,12 @@ GS_API int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t byt
  *                  L1::no_allocate/L2 evict-first
  *   verify_variant 10*U + F (default 10): U as above; F = 0..4 -> plain/nc+L1::no_allocate/.cs/
  *                  nc+L2 evict-first/nc+L2::256B prefetch
- *   ctas_per_sm    grid size of the STG/LDG kernels in CTAs per SM; 0 = resident CTAs (default) */
+ *                  500 + 100*H + 10*C + W : bulk async loads into a shared-memory ring, compare
+ *                  from shared memory. H = 0/1 -> plain / L2 evict-first hint; C = 0/1/2 ->
+ *                  16/32/64 KiB stages; W = 0/1/2 -> 4/8/16 consumer warps
+ *   ctas_per_sm    grid size of the STG/LDG kernels in CTAs per SM; 0 = resident CTAs (default).
+ *                  For the bulk-load verify forms: 2 = two CTAs per SM with half the ring each,
+ *                  anything else = one                                                          */
 GS_API int gs_probe_set_variant(gs_probe *p, int write_variant, int verify_variant,
                                 int ctas_per_sm);
 /* Offered rate (GB/s, whole GPU) the store pass paces itself to; 0 = unpaced.
@@ -473,6 +491,9 @@ GS_API int gs_probe_get_write_rate(const gs_probe *p, uint32_t *gbps, int *is_au
  *     the ranges must have been written before (gs_probe_submit with GS_PROBE_WRITE);
  *   - runs on `stream` (a cudaStream_t; NULL = the default stream) of device
  *     `cuda_ordinal` and returns after that stream has drained; no gs_probe needed;
+ *     the verdicts come back through a cudaMemcpyAsync into ordinary (pageable) host
+ *     memory, which the runtime stages and completes before returning -- the call
+ *     is synchronous by design and pins nothing;
  *   - the first call on each device looks up the array's device address; make that
  *     first call before starting any stream capture;
  *   - every call on a device uses the same array and clears the rows it needs; two

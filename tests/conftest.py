@@ -79,6 +79,12 @@ def pattern_kat():
 
 
 @pytest.fixture(scope="session")
+def pattern_kat_hash():
+    with open(os.path.join(ROOT, "tests", "golden", "pattern_kat.json")) as f:
+        return json.load(f)["hash_vectors"]
+
+
+@pytest.fixture(scope="session")
 def oracle_lib():
     import ctypes
     return ctypes.CDLL(ORACLE_SO)

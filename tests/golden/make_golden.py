@@ -312,13 +312,14 @@ def run_oracle(c):
     return out
 
 
-def pattern_kat():
+def pattern_kat(pattern=0):
     lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "libgs_oracle.so"))
     out = []
     for i, seed in [(0, 0), (1, 0), (0, 1), (255, 1234), (4096, 77), ((1 << 32) - 1, 77),
                     (1 << 32, 77), ((1 << 32) + 5, 0xFFFFFFFF), (11250000000, 20261106)]:
         w = (ctypes.c_uint32 * 4)()
-        lib.gs_oracle_pattern_word(ctypes.c_uint64(i), ctypes.c_uint32(seed), w)
+        assert lib.gs_oracle_pattern_word_p(ctypes.c_uint64(i), ctypes.c_uint32(seed),
+                                            ctypes.c_uint32(pattern), w) == 0
         out.append({"i": i, "seed": seed, "words": list(w)})
     return out
 
@@ -342,7 +343,7 @@ def main():
         json.dump({"generated_by": "tests/golden/make_golden.py",
                    "provenance": "oracle/pattern.c (the probe pattern has no reference "
                                  "counterpart); first vector also checked by hand",
-                   "vectors": pattern_kat()}, f, indent=1)
+                   "vectors": pattern_kat(0), "hash_vectors": pattern_kat(1)}, f, indent=1)
     print("wrote %d cases" % len(CASES))
 
 

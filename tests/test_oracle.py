@@ -50,6 +50,32 @@ def test_pattern_kat(oracle_lib, pattern_kat):
     assert len({tuple(v["words"]) for v in pattern_kat}) == len(pattern_kat)
 
 
+def test_pattern_kat_hash(oracle_lib, pattern_kat_hash):
+    """GS_PROBE_PATTERN_HASH: the oracle against the vectors, and both against an independent
+    restatement of the written definition (csrc/probe_kernels.cuh)."""
+    import ctypes
+    M = 0xFFFFFFFF
+
+    def word(i, seed):
+        lo, hi = i & M, i >> 32
+        h = (lo * 0x9E3779B1 + ((hi ^ seed) * 0x85EBCA77) + seed) & M
+        h ^= h >> 15
+        h = (h * 0x2C1B3C6D) & M
+        h ^= h >> 12
+        rot = ((h << 13) | (h >> 19)) & M
+        return [h, h ^ M, (h * 0x297A2D39 + lo) & M, rot ^ hi ^ 0xC2B2AE3D]
+    for v in pattern_kat_hash:
+        w = (ctypes.c_uint32 * 4)()
+        assert oracle_lib.gs_oracle_pattern_word_p(ctypes.c_uint64(v["i"]), ctypes.c_uint32(v["seed"]),
+                                                   ctypes.c_uint32(1), w) == 0
+        assert list(w) == v["words"] == word(v["i"], v["seed"])
+        assert v["words"][0] ^ v["words"][1] == M                   # both polarities in one word
+    assert pattern_kat_hash[0]["words"] == [0, M, 0, 0xC2B2AE3D]     # i = 0, seed = 0: by hand
+    w = (ctypes.c_uint32 * 4)(1, 2, 3, 4)
+    assert oracle_lib.gs_oracle_pattern_word_p(ctypes.c_uint64(0), ctypes.c_uint32(0), ctypes.c_uint32(2), w) == -1
+    assert list(w) == [1, 2, 3, 4]                                  # unknown pattern: untouched
+
+
 def test_oracle_pattern_check_counts(oracle_lib):
     import ctypes
     n = 1024

@@ -18,11 +18,26 @@ def probe():
     p.close()
 
 
-def oracle_bytes(oracle_lib, nbytes, seed, first=0):
+LOW, HASH = L.GS_PROBE_PATTERN_LOWTOGGLE, L.GS_PROBE_PATTERN_HASH
+# every load+compare form: LDG (unroll x access form) and the bulk-load ring (hint, stage size,
+# consumer warps); the default first
+VERIFY_FORMS = [10, 0, 1, 2, 3, 4, 21, 500, 501, 502, 510, 511, 512, 520, 521, 522, 600, 611, 622]
+
+
+def oracle_bytes(oracle_lib, nbytes, seed, first=0, pattern=LOW):
     buf = (ctypes.c_uint32 * (nbytes // 4))()
-    oracle_lib.gs_oracle_pattern_fill(buf, ctypes.c_uint64(first), ctypes.c_uint64(nbytes // 16),
-                                      ctypes.c_uint32(seed))
+    oracle_lib.gs_oracle_pattern_fill_p(buf, ctypes.c_uint64(first), ctypes.c_uint64(nbytes // 16),
+                                        ctypes.c_uint32(seed), ctypes.c_uint32(pattern))
     return bytes(buf)
+
+
+def oracle_check(oracle_lib, host, seed, pattern=LOW, first=0):
+    mm, fb, fl = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+    arr = (ctypes.c_uint32 * (len(host) // 4)).from_buffer(host)
+    oracle_lib.gs_oracle_pattern_check_p(arr, ctypes.c_uint64(first), ctypes.c_uint64(len(host) // 16),
+                                         ctypes.c_uint32(seed), ctypes.c_uint32(pattern),
+                                         ctypes.byref(mm), ctypes.byref(fb), ctypes.byref(fl))
+    return mm.value, fb.value, fl.value
 
 
 @pytest.mark.parametrize("nbytes", [16, 4096, 64 * 1024, 64 * 1024 + 16, MiB - 16, 3 * MiB + 4080,
@@ -40,14 +55,40 @@ def test_written_pattern_is_bit_exact(probe, oracle_lib, nbytes, wvariant):
         probe.free(d)
 
 
-@pytest.mark.parametrize("vvariant", [0, 1, 2, 3, 4, 10, 21])
-def test_verify_counts_match_oracle(probe, oracle_lib, vvariant):
+@pytest.mark.parametrize("pattern", [LOW, HASH])
+@pytest.mark.parametrize("wvariant", [102, 403, 0])
+@pytest.mark.parametrize("nbytes", [16, 64 * 1024 + 16, 3 * MiB + 4080])
+def test_both_patterns_are_bit_exact_in_one_batch(probe, oracle_lib, nbytes, wvariant, pattern):
+    """The pattern is a property of the slice: a batch mixes both, each slice reads back as its
+    own pattern, and verifying a slice under the other pattern reports every word."""
+    other = HASH if pattern == LOW else LOW
+    d = probe.alloc(2 * nbytes + 256)
+    try:
+        probe.set_variant(write=wvariant)
+        a, b = (d, nbytes, 0xBEEF, 0, pattern), (d + nbytes, nbytes, 0xBEEF, 1, other)
+        v, tm = probe.run([a, b])
+        assert v[0].clean and v[1].clean and tm.launches == 2
+        assert probe.read(d, nbytes) == oracle_bytes(oracle_lib, nbytes, 0xBEEF, pattern=pattern)
+        assert probe.read(d + nbytes, nbytes) == oracle_bytes(oracle_lib, nbytes, 0xBEEF, pattern=other)
+        v, _ = probe.run([(d, nbytes, 0xBEEF, 0, other)], L.GS_PROBE_VERIFY)
+        assert v[0].mismatches == nbytes // 16 and v[0].first_bad_byte == 0
+        with pytest.raises(L.GpushareError) as e:
+            probe.run([(d, nbytes, 1, 0, 2)])
+        assert e.value.status == L.GS_E_INVAL
+    finally:
+        probe.set_variant(write=102)
+        probe.free(d)
+
+
+@pytest.mark.parametrize("pattern", [LOW, HASH])
+@pytest.mark.parametrize("vvariant", VERIFY_FORMS)
+def test_verify_counts_match_oracle(probe, oracle_lib, vvariant, pattern):
     nbytes = 5 * MiB + 48
     d = probe.alloc(nbytes)
     try:
         probe.set_variant(verify=vvariant)
-        probe.run([(d, nbytes, 9)], L.GS_PROBE_WRITE)
-        host = bytearray(oracle_bytes(oracle_lib, nbytes, 9))
+        probe.run([(d, nbytes, 9, 0, pattern)], L.GS_PROBE_WRITE)
+        host = bytearray(oracle_bytes(oracle_lib, nbytes, 9, pattern=pattern))
         for off, mask in [(0, 0x1), (4 * 1000, 0x00010100), (64 * 1024 - 4, 0xFFFFFFFF),
                           (64 * 1024, 0x80000000), (nbytes - 4, 0x3), (nbytes - 16, 0x40),
                           (2 * MiB + 8, 0x8000)]:
@@ -55,17 +96,48 @@ def test_verify_counts_match_oracle(probe, oracle_lib, vvariant):
             word = int.from_bytes(host[off:off + 4], "little") ^ mask
             host[off:off + 4] = word.to_bytes(4, "little")
         assert probe.read(d, nbytes) == bytes(host)
-        mm, fb, fl = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
-        arr = (ctypes.c_uint32 * (nbytes // 4)).from_buffer(host)
-        oracle_lib.gs_oracle_pattern_check(arr, ctypes.c_uint64(0), ctypes.c_uint64(nbytes // 16),
-                                           ctypes.c_uint32(9), ctypes.byref(mm), ctypes.byref(fb),
-                                           ctypes.byref(fl))
-        v, _ = probe.run([(d, nbytes, 9)], L.GS_PROBE_VERIFY)
-        assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == (mm.value, fb.value, fl.value)
-        assert mm.value == 6 and fb.value == 0
+        want = oracle_check(oracle_lib, host, 9, pattern)
+        v, _ = probe.run([(d, nbytes, 9, 0, pattern)], L.GS_PROBE_VERIFY)
+        assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == want
+        assert want[0] == 6 and want[1] == 0
+        if vvariant >= 500:                              # two CTAs per SM, half the ring each
+            probe.set_variant(ctas_per_sm=2)
+            v, _ = probe.run([(d, nbytes, 9, 0, pattern)], L.GS_PROBE_VERIFY)
+            assert (v[0].mismatches, v[0].first_bad_byte, v[0].bit_flips) == want
+    finally:
+        probe.set_variant(verify=10, ctas_per_sm=0)
+        probe.free(d)
+
+
+@pytest.mark.parametrize("vvariant", [500, 511, 522, 620, 10])
+def test_load_pass_on_ragged_batches(probe, oracle_lib, vvariant):
+    """Ragged slices (sub-chunk, sub-tile, one word, tile + one word) in one batch: a fault in the
+    very last word and in the first word of each is found at its byte, by every load form."""
+    sizes = [16, 48, 16 * 1024 - 16, 16 * 1024 + 16, 32 * 1024, 64 * 1024 - 16, 64 * 1024 + 16,
+             5 * 64 * 1024 + 4096 + 16, 3 * MiB]
+    arena = probe.alloc(sum(sizes) + 256)
+    try:
+        slices, off = [], 0
+        for k, n in enumerate(sizes):
+            slices.append((arena + off, n, 40 + k, k, k % 2))
+            off += n
+        probe.set_variant(verify=vvariant)
+        v, _ = probe.run(slices)
+        assert all(x.clean for x in v)
+        for (base, n, seed, _k, pat) in slices:
+            assert probe.read(base, n) == oracle_bytes(oracle_lib, n, seed, pattern=pat)
+        for (base, n, _s, _k, _p) in slices:
+            probe.inject(base, n - 4, 0x80000001)
+        v, _ = probe.run(slices, L.GS_PROBE_VERIFY)
+        assert [(x.mismatches, x.first_bad_byte, x.bit_flips) for x in v] == [(1, n - 4, 2) for n in sizes]
+        for (base, n, _s, _k, _p) in slices:
+            probe.inject(base, n - 4, 0x80000001)
+            probe.inject(base, 0, 0x100)
+        v, _ = probe.run(slices, L.GS_PROBE_VERIFY)
+        assert [(x.mismatches, x.first_bad_byte, x.bit_flips) for x in v] == [(1, 1, 1)] * len(sizes)
     finally:
         probe.set_variant(verify=10)
-        probe.free(d)
+        probe.free(arena)
 
 
 def test_wrong_seed_is_all_mismatch(probe):

@@ -5,12 +5,15 @@ whose memory is granted to tenants down to the last unit (an allocation would fa
 take what a tenant was promised), and callers that cannot afford the device-wide
 synchronisation cudaMalloc/cudaFree imply. For them the verdict table is a fixed array
 on the device. This file checks, through the C ABI, that the verdicts equal those of the
-ordinary entry point (gs_probe_run with GS_PROBE_VERIFY) bit for bit -- the probe is
-integer work, so the tolerance is zero -- on two calls in a row, the second of which
-must not see anything the first left in the shared array.
+ordinary entry point (gs_probe_run with GS_PROBE_VERIFY) and those the CPU oracle
+(oracle/pattern.c) computes from a read-back of the same memory, bit for bit -- the
+probe is integer work, so the tolerance is zero -- on two calls in a row, the second of
+which must not see anything the first left in the shared array.
 
 Collected last on purpose (conftest keeps test_zz_* at the end).
 """
+
+import ctypes
 
 import pytest
 
@@ -22,13 +25,29 @@ MiB = 1 << 20
 
 
 def _noalloc(lib, slices):
-    arr = (L.Slice * len(slices))(*[L.Slice(b, n, s, i) for i, (b, n, s) in enumerate(slices)])
+    arr = (L.Slice * len(slices))(*[L.Slice(s[0], s[1], s[2], i, s[4] if len(s) > 4 else 0, 0)
+                                    for i, s in enumerate(slices)])
     res = (L.SliceResult * len(slices))()
     rc = lib.gs_probe_verify_noalloc(0, None, arr, len(slices), res)
     return rc, [(r.mismatches, r.first_bad_byte, r.bit_flips) for r in res]
 
 
-def test_noalloc_verdicts_equal_ordinary_entry_point_twice():
+def _oracle_verdicts(oracle_lib, p, slices):
+    """What the CPU restatement says about the bytes that are in the slices right now."""
+    out = []
+    for k, s in enumerate(slices):
+        base, n, seed = s[0], s[1], s[2]
+        host = bytearray(p.read(base, n))
+        arr = (ctypes.c_uint32 * (n // 4)).from_buffer(host)
+        mm, fb, fl = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+        oracle_lib.gs_oracle_pattern_check_p(arr, ctypes.c_uint64(0), ctypes.c_uint64(n // 16),
+                                             ctypes.c_uint32(seed), ctypes.c_uint32(k % 2),
+                                             ctypes.byref(mm), ctypes.byref(fb), ctypes.byref(fl))
+        out.append((mm.value, fb.value, fl.value))
+    return out
+
+
+def test_noalloc_verdicts_equal_ordinary_entry_point_twice(oracle_lib):
     from gpushare_b200.probe import Probe
     lib = L.load()
     sizes = [3 * MiB + 48, 64 * 1024, 9 * MiB, 16, 2 * MiB]
@@ -37,7 +56,7 @@ def test_noalloc_verdicts_equal_ordinary_entry_point_twice():
         try:
             slices, off = [], 0
             for k, n in enumerate(sizes):
-                slices.append((arena + off, n, 500 + k))
+                slices.append((arena + off, n, 500 + k, k, k % 2))    # both patterns
                 off += n
             p.run(slices, L.GS_PROBE_WRITE)
 
@@ -49,6 +68,7 @@ def test_noalloc_verdicts_equal_ordinary_entry_point_twice():
             rc, got = _noalloc(lib, slices)
             assert rc == L.GS_OK
             assert got == want
+            assert got == _oracle_verdicts(oracle_lib, p, slices)
             assert [g[0] for g in got] == [1, 0, 1, 0, 0] and got[0][2] == 5
 
             # call 2: repair those, break slices 1, 3 and 4 -- rows 0 and 2 of the shared
@@ -63,6 +83,7 @@ def test_noalloc_verdicts_equal_ordinary_entry_point_twice():
             rc, got = _noalloc(lib, slices)
             assert rc == L.GS_OK
             assert got == want
+            assert got == _oracle_verdicts(oracle_lib, p, slices)
             assert [g[0] for g in got] == [0, 1, 0, 1, 1]
             assert got[0] == (0, 2**64 - 1, 0) and got[3] == (1, 14, 16)
 
