@@ -21,9 +21,8 @@ FAKE_NVML := tests/fake_nvml/libfake_nvml.so
 
 DAEMON    := $(PKG)/bin/gpushare-device-plugin-v2
 INSPECT   := $(PKG)/bin/kubectl-inspect-gpushare-v2
-PODGETTER := $(PKG)/bin/podgetter
 
-all: $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON) $(INSPECT) $(PODGETTER)
+all: $(CORE_SO) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON) $(INSPECT)
 
 $(CSRC)/%.o: $(CSRC)/%.cpp include/gpushare.h $(wildcard $(CSRC)/*.h)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
@@ -45,11 +44,6 @@ $(INSPECT): $(wildcard $(PKG)/daemon_cpp/*.cpp $(PKG)/daemon_cpp/*.h) include/gp
 	$(CXX) -O2 -g -std=c++17 -Wall -Wextra -Iinclude -I$(PKG)/daemon_cpp $(PKG)/daemon_cpp/inspect_main.cpp -o $@ \
 		-L$(PKG) -lgpushare_core -Wl,-rpath,'$$ORIGIN/..' -lssl -lcrypto -lpthread
 
-$(PODGETTER): $(wildcard $(PKG)/daemon_cpp/*.cpp $(PKG)/daemon_cpp/*.h) include/gpushare.h $(CORE_SO)
-	mkdir -p $(PKG)/bin
-	$(CXX) -O2 -g -std=c++17 -Wall -Wextra -Iinclude -I$(PKG)/daemon_cpp $(PKG)/daemon_cpp/podgetter_main.cpp -o $@ \
-		-L$(PKG) -lgpushare_core -Wl,-rpath,'$$ORIGIN/..' -lssl -lcrypto -lpthread
-
 # Oracle: CPU restatement used ONLY by tests/, smoke() and bench.py's cpu_baseline leg.
 ORACLE_OBJS := $(patsubst %.c,%.o,$(wildcard oracle/*.c)) $(patsubst %.cpp,%.o,$(wildcard oracle/*.cpp))
 oracle/%.o: oracle/%.c
@@ -63,7 +57,7 @@ $(FAKE_NVML): tests/fake_nvml/fake_nvml.c
 	$(CC) $(CFLAGS) -shared -o $@ $< -lpthread
 
 clean:
-	rm -f $(OBJS) $(CORE_SO) $(ORACLE_OBJS) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON) $(INSPECT) $(PODGETTER)
+	rm -f $(OBJS) $(CORE_SO) $(ORACLE_OBJS) $(ORACLE_SO) $(FAKE_NVML) $(DAEMON) $(INSPECT)
 
 test: all
 	python -m pytest tests -q -m "not gpu"

@@ -173,6 +173,8 @@ SIGNATURES = {
     "gs_probe_mem_alloc": (_int, [_vp, _u64, _P(_vp)]),
     "gs_probe_mem_free": (_int, [_vp, _vp]),
     "gs_probe_mem_info": (_int, [_vp, _P(_u64), _P(_u64)]),
+    "gs_probe_test_skip_stores": (_int, [_vp, _int]),
+    "gs_probe_next_seed": (_int, [_vp, _P(_u32)]),
     "gs_probe_submit": (_int, [_vp, _P(Slice), _u32, _u32]),
     "gs_probe_wait": (_int, [_vp, _P(SliceResult), _u32, _P(ProbeTiming)]),
     "gs_probe_poll": (_int, [_vp]),

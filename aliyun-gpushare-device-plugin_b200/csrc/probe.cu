@@ -8,6 +8,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
+#include <unistd.h>
 
 #include <mutex>
 
@@ -145,7 +147,29 @@ struct gs_probe {
   int verify_variant = 10;  // U = 2, plain ld.global.v4: 30 registers, 8 CTAs/SM resident;
                             // best sustained rate after a store pass (tools/probe_sustained_grid.py)
   int ctas_per_sm = 0;      // STG/LDG kernels: CTAs per SM in the grid; 0 = occupancy query
+  // test hook (gs_probe_test_skip_stores): store passes from the skip_stores_from-th on (1-based)
+  // launch nothing; 0 = never
+  uint32_t skip_stores_from = 0;
+  uint32_t store_passes = 0;
+  uint32_t seed_nonce = 0;  // drawn when the engine is opened
+  uint32_t seed_count = 0;  // sweeps seeded so far
 };
+
+// Something that differs between two engines and between two runs of the process: the
+// monotonic clock, the pid and the engine's address, avalanched.
+static uint32_t fresh_nonce() {
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  static int salt;
+  uint64_t x = (uint64_t)ts.tv_nsec ^ ((uint64_t)ts.tv_sec << 30) ^ ((uint64_t)getpid() << 17) ^
+               (uint64_t)(uintptr_t)&salt ^ ((uint64_t)++salt << 48);
+  x ^= x >> 33;
+  x *= 0xFF51AFD7ED558CCDull;
+  x ^= x >> 33;
+  x *= 0xC4CEB9FE1A85EC53ull;
+  x ^= x >> 33;
+  return (uint32_t)x;
+}
 
 #define GS_CUDA(call)                                      \
   do {                                                     \
@@ -176,6 +200,8 @@ int gs_probe_open(int cuda_ordinal, gs_probe **out) {
     return GS_E_CUDA;
   }
   p->dev = cuda_ordinal;
+  p->seed_nonce = fresh_nonce();
+  if (const char *m = getenv("GS_PROBE_TEST_SKIP_STORES")) p->skip_stores_from = (uint32_t)atoi(m);
   if (const char *m = getenv("GS_PROBE_SCRUB_MODE")) p->scrub_mode = (uint32_t)atoi(m);
   cudaError_t e = cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, cuda_ordinal);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking);
@@ -209,6 +235,19 @@ int gs_probe_close(gs_probe *p) {
 int gs_probe_sm_count(const gs_probe *p, int *sms) {
   if (!p || !sms) return GS_E_INVAL;
   *sms = p->sms;
+  return GS_OK;
+}
+
+int gs_probe_test_skip_stores(gs_probe *p, int on) {
+  if (!p) return GS_E_INVAL;
+  p->skip_stores_from = on ? p->store_passes + 1 : 0;
+  return GS_OK;
+}
+
+int gs_probe_next_seed(gs_probe *p, uint32_t *seed) {
+  if (!p || !seed) return GS_E_INVAL;
+  // nonce + odd multiple of the counter: 2^32 distinct values before the first repeat
+  *seed = p->seed_nonce + 0x9E3779B1u * ++p->seed_count;
   return GS_OK;
 }
 
@@ -357,7 +396,11 @@ int gs_probe_submit(gs_probe *p, const gs_slice *slices, uint32_t n, uint32_t pa
   uint32_t launches = 0;
   GS_CUDA(cudaMemsetAsync(p->d_res, 0, sizeof(DevResult) * n, p->stream));
   GS_CUDA(cudaEventRecord(p->ev[0], p->stream));
-  if ((passes & GS_PROBE_WRITE) && is_paced_code(p->write_variant)) {
+  if (passes & GS_PROBE_WRITE) ++p->store_passes;
+  if ((passes & GS_PROBE_WRITE) && p->skip_stores_from && p->store_passes >= p->skip_stores_from) {
+    // test hook: a store pass that silently does nothing; the load pass must then report the
+    // range (a fresh seed never matches what an earlier sweep left behind)
+  } else if ((passes & GS_PROBE_WRITE) && is_paced_code(p->write_variant)) {
     const uint32_t sub_vec = kPacedSubVec[p->write_variant - kWritePacedBase];
     const uint64_t grid = tiles < (uint64_t)p->sms ? tiles : (uint64_t)p->sms;
     uint32_t period_x16 = 0;  // per token of sub_vec words, so that `grid` CTAs offer write_rate_gbps

@@ -1,9 +1,16 @@
-"""gpushare-device-plugin-v2 -- the daemon entry point (cmd/nvidia/main.go, gpumanager.go).
+"""The node daemon's host logic in Python -- a TEST HARNESS, not the product.
+
+The daemon that ships is the native binary (daemon_cpp/main.cpp -> bin/gpushare-device-plugin-v2,
+what deploy/ runs). This twin exists because the retry-ladder and supervisor tests inject their
+sleeps, clocks and fake sources here, and because it reads as a specification of
+cmd/nvidia/main.go and gpumanager.go. It serves the same library over the same transport, but it
+does NOT carry the slice probe: the probe worker (batching, concurrent health sweeps, the
+no-allocation read-back) lives in the binary only, so there is one implementation to keep right.
 
 Keeps the reference's command line (flag names, defaults, single- or double-dash forms as
 Go's `flag` accepts) and environment (NODE_NAME mandatory, podmanager.go:55-58), and wires
 the hot path: NVML enumerate -> device table -> plugin -> gRPC server -> Register ->
-XID health watch -> probe at Allocate time.
+XID health watch.
 
 Pod source: by default the live one (k8s_io: kubelet /pods or apiserver LIST with the
 reference's retry ladders, PATCH with its one retry; KUBECONFIG or the in-cluster service
@@ -22,7 +29,6 @@ import ctypes
 import faulthandler
 import json
 import os
-import queue
 import select
 import signal
 import struct
@@ -63,9 +69,8 @@ def parse_args(argv=None):
     flag("pod-source-file", default="", help="JSON file with the node's pods (stands in for the lister)")
     flag("nvml-lib", default="", help="path of libnvidia-ml (tests: the fake NVML)")
     flag("socket-dir", default=os.path.dirname(SERVER_SOCK), help="device-plugins directory")
-    boolflag("probe", "sweep each granted slice on the GPU after Allocate")
-    flag("health-probe-interval", type=int, default=0,
-         help="with --probe and --health-check: every N seconds sweep each GPU's free memory (0 = off)")
+    boolflag("probe", "(native binary only) sweep each granted slice on the GPU after Allocate")
+    flag("health-probe-interval", type=int, default=0, help="(native binary only)")
     boolflag("no-register", "serve without registering with kubelet (harness)")
     flag("transport", default="native", choices=("native", "grpcio"),
          help="gRPC transport: the library's own HTTP/2 server (native) or Python grpcio")
@@ -75,6 +80,9 @@ def parse_args(argv=None):
         if v not in ("true", "false", "1", "0", "t", "f"):
             ap.error("invalid boolean value %r for -%s" % (getattr(a, k), k.replace("_", "-")))
         setattr(a, k, v in ("true", "1", "t"))
+    if a.probe or a.health_probe_interval:
+        ap.error("the slice probe runs in the native daemon (bin/gpushare-device-plugin-v2) only; "
+                 "this Python twin is the test harness of the host logic")
     return a
 
 
@@ -164,19 +172,9 @@ class PluginInstance:
             self.plugin = k8s_io.ClusterDevicePlugin(
                 self.table, node, k8s_io.PodLister(transport, node, a.query_kubelet), transport, cgpu)
 
-        self.probes = {}
-        if a.probe:
-            from .probe import Probe, ProbeScheduler
-            for info, o in zip(infos, nv.map_cuda_ordinals(infos)):
-                if o >= 0:
-                    self.probes[info.nvml_index] = ProbeScheduler(
-                        Probe(o), on_bad=lambda tag, v, g=info.nvml_index: self.plugin.unhealthy(g))
-        self.unit_bytes = (1 << 20) if unit == api.MiB else (1 << 30)
-        self.arenas = {}
-        self.probe_queue = queue.Queue()
-        self.probe_thread = None
-        self._allocate = self.plugin.Allocate
-        self.plugin.Allocate = self.allocate_and_probe
+        if self.source is not None:
+            self._allocate = self.plugin.Allocate
+            self.plugin.Allocate = self.allocate_from_file
         if a.transport == "native":
             from .native_transport import NativeDevicePluginServer as server_cls
         else:
@@ -184,51 +182,9 @@ class PluginInstance:
         self.server = server_cls(self.plugin, os.path.join(a.socket_dir, os.path.basename(SERVER_SOCK)))
         self.stop = threading.Event()
 
-    def allocate_and_probe(self, request):
-        if self.source is not None:
-            self.plugin.set_pods(self.source.list())
-        d = self._allocate(request)
-        if d.kind == "matched" and d.gpu_index in self.probes:
-            # the answer is already decided; the sweep is queued for the probe thread and can
-            # neither delay nor change it (parity)
-            self.probe_queue.put((d.gpu_index, d.pod_req_units * self.unit_bytes, d.pod_index))
-        return d
-
-    def probe_worker(self):
-        """Owns every CUDA call of the daemon: sweeps granted ranges as they arrive, harvests
-        verdicts, and runs the health-time sweep on its timer."""
-        last_sweep = time.time()
-        while not self.stop.is_set():
-            try:
-                g, nbytes, pod_index = self.probe_queue.get(timeout=0.2)
-            except queue.Empty:
-                g = None
-            if g is not None:
-                sched = self.probes[g]
-                try:
-                    sched.drain()                        # one arena per GPU: finish the previous sweep
-                    old = self.arenas.pop(g, None)
-                    if old:
-                        sched.probe.free(old)
-                    free, _ = sched.probe.mem_info()
-                    # exactly the granted range, capped by what is free right now
-                    nbytes = min(nbytes, max(0, free - (1 << 30))) & ~0xFFFFF
-                    if nbytes:
-                        self.arenas[g] = sched.probe.alloc(nbytes)
-                        sched.grant(self.arenas[g], nbytes, pod_index & 0xFFFFFFFF, pod_index)
-                        sched.pump()
-                        log(self.a.v, 1, "probe: gpu %d, %d bytes granted to pod %d queued for a sweep" % (
-                            g, nbytes, pod_index))
-                except L.GpushareError as e:
-                    log(self.a.v, 1, "probe skipped: %s" % e)
-            for g2, s in self.probes.items():
-                s.pump()
-                # the range belongs to the tenant: give it back the moment the sweep is over
-                if s.inflight is None and not s.pending and g2 in self.arenas:
-                    s.probe.free(self.arenas.pop(g2))
-            if self.a.health_probe_interval and time.time() - last_sweep >= self.a.health_probe_interval:
-                last_sweep = time.time()
-                self.health_sweep()
+    def allocate_from_file(self, request):
+        self.plugin.set_pods(self.source.list())     # the file stands in for the lister: re-read per Allocate
+        return self._allocate(request)
 
     def Serve(self):
         a = self.a
@@ -237,9 +193,6 @@ class PluginInstance:
         else:
             self.server.Serve(os.path.join(a.socket_dir, os.path.basename(KUBELET_SOCKET)))
         log(a.v, 1, "Starting to serve on %s" % self.server.socket)
-        if self.probes:
-            self.probe_thread = threading.Thread(target=self.probe_worker, daemon=True)
-            self.probe_thread.start()
         if a.health_check:                                          # server.go:211-229
             bad_mask = self.nv.health_open()
             for g in range(len(self.infos)):
@@ -254,37 +207,12 @@ class PluginInstance:
             self.pump_thread = threading.Thread(target=pump, daemon=True)
             self.pump_thread.start()
 
-    def health_sweep(self):
-        """Health-time probe: everything that is free on each GPU right now, minus a margin
-        (tenants' memory is theirs). A mismatch marks the whole GPU unhealthy."""
-        for g, sched in self.probes.items():
-            if sched.inflight is not None or sched.pending:
-                continue                                # an Allocate-time sweep is running
-            try:
-                verdict, tm = sched.probe.sweep_free(margin_bytes=2 << 30)
-            except L.GpushareError as e:
-                log(self.a.v, 1, "health probe skipped on gpu %d: %s" % (g, e))
-                continue
-            if verdict is None:
-                continue
-            log(self.a.v, 1, "health probe: gpu %d swept %d bytes at %.0f GB/s, %d mismatching words" % (
-                g, tm.bytes, tm.gbps(), verdict.mismatches))
-            if not verdict.clean:
-                self.plugin.unhealthy(g)
-
     def Stop(self):
         self.stop.set()
         self.server.Stop()
         if self.a.health_check:
             self.pump_thread.join(3)
             self.nv.health_close()
-        if self.probe_thread is not None:
-            self.probe_thread.join(10)
-        for g, sched in self.probes.items():
-            sched.drain()
-            if g in self.arenas:
-                sched.probe.free(self.arenas[g])
-            sched.probe.close()
 
 
 def coredump(path):

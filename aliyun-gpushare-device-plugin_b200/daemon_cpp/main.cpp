@@ -150,7 +150,13 @@ Flags parse_flags(int argc, char **argv) {
 }
 
 // ---- the slice probe beside Allocate (no counterpart in the reference) --------------------------
-// One worker owns every CUDA call: a grant is swept after its answer left, never before.
+// One worker thread owns every CUDA call and never waits for a sweep: a grant is queued when its
+// answer has left, the worker gathers what has queued up for a GPU into one batch (at most
+// GS_PROBE_MAX_SLICES slices per launch pair, an L2 scrub between the passes when the batch is
+// smaller than the L2 can hide), submits it and goes on; finished batches are collected by
+// polling. Health-time sweeps of free memory start on every idle GPU at once and are collected the
+// same way, so a node's sweep takes one GPU's time, not the sum. Every sweep draws its seeds from
+// the engine (gs_probe_next_seed): what an earlier sweep left in a range never matches.
 struct ProbeJob {
   int gpu;
   uint64_t bytes;
@@ -158,9 +164,26 @@ struct ProbeJob {
 };
 
 struct ProbeWorker {
-  std::map<int, gs_probe *> probes;  // NVML index -> engine
-  std::map<int, void *> arenas;
-  std::map<int, bool> inflight;
+  static constexpr uint64_t kScrubBelow = 512ull << 20;     // batch bytes below which the L2 is scrubbed
+  static constexpr uint64_t kGrantMargin = 1ull << 30;      // free HBM left alone when sweeping a grant
+  static constexpr uint64_t kHealthMargin = 2ull << 30;     // ... when sweeping free memory
+  static constexpr uint64_t kSentinelBytes = 64ull << 20;   // kept per GPU for the no-allocation read-back
+
+  struct Gpu {
+    gs_probe *probe = nullptr;
+    int cuda_ordinal = -1;
+    uint64_t total_bytes = 0;
+    uint64_t granted_bytes = 0;          // handed to tenants through this plugin since it started
+    std::deque<ProbeJob> pending;        // grants waiting for the engine
+    std::vector<void *> arenas;          // ranges of the batch in flight (returned when it ends)
+    std::vector<int32_t> tags;
+    bool inflight = false;
+    bool inflight_is_health = false;
+    void *sentinel = nullptr;            // written once at start, read back without allocating
+    uint32_t sentinel_seed = 0;
+    uint64_t dropped = 0;
+  };
+  std::map<int, Gpu> gpus;  // NVML index -> state
   std::mutex mu;
   std::condition_variable cv;
   std::deque<ProbeJob> queue;
@@ -170,98 +193,205 @@ struct ProbeWorker {
   gs_plugin *plugin = nullptr;
   long health_interval = 0;
 
+  void add_gpu(int nvml_index, int cuda_ordinal, uint64_t total_bytes, gs_probe *p) {
+    Gpu &g = gpus[nvml_index];
+    g.probe = p;
+    g.cuda_ordinal = cuda_ordinal;
+    g.total_bytes = total_bytes;
+  }
   void mark_bad(int gpu) {
     gs_law_mark_unhealthy_gpu(table, gpu);
     gs_plugin_notify_health(plugin);
   }
-  void harvest(int gpu, bool block, const char *label = "probe") {
-    if (!inflight[gpu]) return;
-    gs_probe *p = probes[gpu];
-    if (!block && gs_probe_poll(p) != GS_OK) return;
-    gs_slice_result r;
-    gs_probe_timing tm;
-    if (gs_probe_wait(p, &r, 1, &tm) == GS_OK) {
-      const double ms = tm.write_ms + tm.verify_ms + tm.scrub_ms;
-      logv(1, "%s: gpu %d swept %llu bytes at %.0f GB/s, %llu mismatching words", label, gpu,
-           (unsigned long long)tm.bytes, ms > 0 ? 2.0 * (double)tm.bytes / ms / 1e6 : 0.0,
-           (unsigned long long)r.mismatches);
-      if (r.mismatches) mark_bad(gpu);
-    }
-    inflight[gpu] = false;
-    // the range belongs to the tenant: give it back the moment the sweep is over
-    if (arenas.count(gpu)) {
-      gs_probe_mem_free(p, arenas[gpu]);
-      arenas.erase(gpu);
-    }
+  void release(Gpu &g) {
+    // the ranges belong to the tenants: give them back the moment the sweep is over
+    for (void *d : g.arenas) gs_probe_mem_free(g.probe, d);
+    g.arenas.clear();
+    g.tags.clear();
+    g.inflight = false;
   }
-  void start(const ProbeJob &j) {
-    gs_probe *p = probes[j.gpu];
-    harvest(j.gpu, true);  // one arena per GPU: finish the previous sweep
-    if (arenas.count(j.gpu)) {
-      gs_probe_mem_free(p, arenas[j.gpu]);
-      arenas.erase(j.gpu);
+  void harvest(int idx, Gpu &g, bool block) {
+    if (!g.inflight) return;
+    if (!block && gs_probe_poll(g.probe) != GS_OK) return;
+    gs_slice_result r[GS_PROBE_MAX_SLICES];
+    gs_probe_timing tm;
+    const char *label = g.inflight_is_health ? "health probe" : "probe";
+    if (gs_probe_wait(g.probe, r, GS_PROBE_MAX_SLICES, &tm) == GS_OK) {
+      const double ms = tm.write_ms + tm.verify_ms + tm.scrub_ms;
+      unsigned long long bad = 0;
+      for (size_t i = 0; i < g.arenas.size(); ++i) bad += r[i].mismatches;
+      logv(1, "%s: gpu %d swept %llu bytes in %zu slice(s), %u launches, at %.0f GB/s, %llu mismatching words", label,
+           idx, (unsigned long long)tm.bytes, g.arenas.size(), tm.launches,
+           ms > 0 ? 2.0 * (double)tm.bytes / ms / 1e6 : 0.0, bad);
+      if (bad) mark_bad(idx);
+    } else {
+      logv(1, "%s: gpu %d: %s", label, idx, gs_cuda_last_error());
     }
-    uint64_t free_b = 0, total_b = 0;
-    if (gs_probe_mem_info(p, &free_b, &total_b) != GS_OK) return;
-    uint64_t n = j.bytes;  // exactly the granted range, capped by what is free right now
-    const uint64_t room = free_b > (1ull << 30) ? free_b - (1ull << 30) : 0;
-    if (n > room) n = room;
-    n &= ~0xFFFFFull;
+    release(g);
+  }
+  // the grants queued for one GPU -> one batch -> one launch pair
+  void start_grants(int idx, Gpu &g) {
+    if (g.inflight || g.pending.empty()) return;
+    gs_slice sl[GS_PROBE_MAX_SLICES];
+    memset(sl, 0, sizeof(sl));
+    uint32_t n = 0;
+    uint64_t total = 0;
+    while (!g.pending.empty() && n < GS_PROBE_MAX_SLICES) {
+      const ProbeJob j = g.pending.front();
+      g.pending.pop_front();
+      uint64_t free_b = 0, total_b = 0;
+      if (gs_probe_mem_info(g.probe, &free_b, &total_b) != GS_OK) break;
+      uint64_t bytes = j.bytes;  // exactly the granted range, capped by what is free right now
+      const uint64_t room = free_b > kGrantMargin ? free_b - kGrantMargin : 0;
+      if (bytes > room) bytes = room;
+      bytes &= ~0xFFFFFull;
+      if (!bytes) {
+        logv(1, "probe skipped: gpu %d has no free memory left for the %llu bytes granted to pod %d", idx,
+             (unsigned long long)j.bytes, j.pod_index);
+        continue;
+      }
+      void *d = nullptr;
+      if (gs_probe_mem_alloc(g.probe, bytes, &d) != GS_OK) {
+        logv(1, "probe skipped: %s", gs_cuda_last_error());
+        continue;
+      }
+      g.arenas.push_back(d);
+      g.tags.push_back(j.pod_index);
+      sl[n].base = d;
+      sl[n].bytes = bytes;
+      gs_probe_next_seed(g.probe, &sl[n].seed);
+      sl[n].tag = (uint32_t)j.pod_index;
+      sl[n].pattern = GS_PROBE_PATTERN_LOWTOGGLE;
+      total += bytes;
+      logv(1, "probe: gpu %d, %llu bytes granted to pod %d queued for a sweep", idx, (unsigned long long)bytes,
+           j.pod_index);
+      ++n;
+    }
     if (!n) return;
-    void *d = nullptr;
-    if (gs_probe_mem_alloc(p, n, &d) != GS_OK) {
+    uint32_t passes = GS_PROBE_WRITE | GS_PROBE_VERIFY;
+    if (total < kScrubBelow) passes |= GS_PROBE_SCRUB;
+    if (gs_probe_submit(g.probe, sl, n, passes) != GS_OK) {
       logv(1, "probe skipped: %s", gs_cuda_last_error());
+      release(g);  // nothing was launched: the ranges go back at once
       return;
     }
-    arenas[j.gpu] = d;
+    g.inflight = true;
+    g.inflight_is_health = false;
+    logv(1, "probe: gpu %d, %u slice(s), %llu bytes in one launch pair", idx, n, (unsigned long long)total);
+  }
+  // Health-time probe. What may be written is memory nobody was promised: free HBM minus a
+  // margin, and never more than the GPU's total minus what this plugin has granted (a tenant
+  // that has not yet grown into its grant must still find it). The sweep covers HBM that is free
+  // now -- not the pages a tenant will later get. Started on every idle GPU, collected by poll.
+  void start_health(int idx, Gpu &g) {
+    if (g.inflight || !g.pending.empty()) return;
+    uint64_t free_b = 0, total_b = 0;
+    if (gs_probe_mem_info(g.probe, &free_b, &total_b) != GS_OK) return;
+    const uint64_t unreserved = g.total_bytes > g.granted_bytes ? g.total_bytes - g.granted_bytes : 0;
+    uint64_t bytes = free_b < unreserved ? free_b : unreserved;
+    bytes = bytes > kHealthMargin ? (bytes - kHealthMargin) & ~0xFFFFFull : 0;
+    if (bytes < (1ull << 30)) {
+      sentinel_check(idx, g);  // nothing left to sweep: read the resident range back, allocating nothing
+      return;
+    }
+    void *d = nullptr;
+    if (gs_probe_mem_alloc(g.probe, bytes, &d) != GS_OK) {
+      logv(1, "health probe skipped: %s", gs_cuda_last_error());
+      sentinel_check(idx, g);
+      return;
+    }
     gs_slice s;
     memset(&s, 0, sizeof(s));
     s.base = d;
-    s.bytes = n;
-    s.seed = (uint32_t)j.pod_index;
-    s.tag = (uint32_t)j.pod_index;
-    uint32_t passes = GS_PROBE_WRITE | GS_PROBE_VERIFY;
-    if (n < (512ull << 20)) passes |= GS_PROBE_SCRUB;
-    if (gs_probe_submit(p, &s, 1, passes) == GS_OK) {
-      inflight[j.gpu] = true;
-      logv(1, "probe: gpu %d, %llu bytes granted to pod %d queued for a sweep", j.gpu, (unsigned long long)n,
-           j.pod_index);
+    s.bytes = bytes;
+    gs_probe_next_seed(g.probe, &s.seed);
+    s.pattern = GS_PROBE_PATTERN_HASH;  // the strong pattern: nobody is waiting for this sweep
+    g.arenas.push_back(d);
+    g.tags.push_back(-1);
+    if (gs_probe_submit(g.probe, &s, 1, GS_PROBE_WRITE | GS_PROBE_VERIFY) != GS_OK) {
+      logv(1, "health probe skipped: %s", gs_cuda_last_error());
+      release(g);
+      return;
     }
+    g.inflight = true;
+    g.inflight_is_health = true;
   }
-  // health-time probe: what is free on each idle GPU right now, minus a margin
-  void health_sweep() {
-    for (auto &kv : probes) {
-      if (inflight[kv.first]) continue;
-      uint64_t free_b = 0, total_b = 0;
-      if (gs_probe_mem_info(kv.second, &free_b, &total_b) != GS_OK || free_b < (3ull << 30)) continue;
-      ProbeJob j{kv.first, free_b - (2ull << 30), 0x5eed};
-      start(j);
-      harvest(kv.first, true, "health probe");
+  // A GPU granted out to the last unit leaves the health checker nothing to allocate. A small range
+  // taken and written once while the GPU was still empty is read back instead through the entry
+  // point that allocates nothing (gs_probe_verify_noalloc): the whole path -- launch, loads from
+  // HBM, compare, verdict -- still answers, and the range itself must still hold what was written.
+  void sentinel_setup(int idx, Gpu &g) {
+    void *d = nullptr;
+    if (gs_probe_mem_alloc(g.probe, kSentinelBytes, &d) != GS_OK) return;
+    gs_slice s;
+    memset(&s, 0, sizeof(s));
+    s.base = d;
+    s.bytes = kSentinelBytes;
+    gs_probe_next_seed(g.probe, &s.seed);
+    s.pattern = GS_PROBE_PATTERN_HASH;
+    gs_slice_result r;
+    if (gs_probe_run(g.probe, &s, 1, GS_PROBE_WRITE | GS_PROBE_VERIFY, &r, nullptr) != GS_OK || r.mismatches) {
+      logv(1, "health probe: gpu %d: sentinel range could not be written", idx);
+      gs_probe_mem_free(g.probe, d);
+      return;
     }
+    g.sentinel = d;
+    g.sentinel_seed = s.seed;
+  }
+  void sentinel_check(int idx, Gpu &g) {
+    if (!g.sentinel) return;
+    gs_slice s;
+    memset(&s, 0, sizeof(s));
+    s.base = g.sentinel;
+    s.bytes = kSentinelBytes;
+    s.seed = g.sentinel_seed;
+    s.pattern = GS_PROBE_PATTERN_HASH;
+    gs_slice_result r;
+    const int rc = gs_probe_verify_noalloc(g.cuda_ordinal, nullptr, &s, 1, &r);
+    if (rc != GS_OK) {
+      logv(1, "health probe: gpu %d: %s", idx, gs_cuda_last_error());
+      return;
+    }
+    logv(1, "health probe: gpu %d sentinel of %llu bytes read back without allocating, %llu mismatching words", idx,
+         (unsigned long long)kSentinelBytes, (unsigned long long)r.mismatches);
+    if (r.mismatches) mark_bad(idx);
   }
   void run() {
+    for (auto &kv : gpus) sentinel_setup(kv.first, kv.second);
     time_t last = time(nullptr);
     while (!stop.load()) {
-      ProbeJob j{-1, 0, 0};
+      bool busy = false;
+      for (auto &kv : gpus) busy |= kv.second.inflight;
       {
         std::unique_lock<std::mutex> lk(mu);
-        cv.wait_for(lk, std::chrono::milliseconds(200), [&] { return stop.load() || !queue.empty(); });
-        if (!queue.empty()) {
-          j = queue.front();
+        // while a sweep is in flight come back soon to collect it; otherwise sleep until a grant arrives
+        cv.wait_for(lk, std::chrono::milliseconds(busy ? 2 : 200), [&] { return stop.load() || !queue.empty(); });
+        while (!queue.empty()) {
+          const ProbeJob j = queue.front();
           queue.pop_front();
+          auto it = gpus.find(j.gpu);
+          if (it == gpus.end()) continue;
+          Gpu &g = it->second;
+          g.granted_bytes += j.bytes;
+          if (g.pending.size() >= GS_PROBE_MAX_SLICES) {  // HBM cannot be swept as fast as it is granted:
+            g.pending.pop_front();                        // the newest grants win, the rest are counted
+            ++g.dropped;
+          }
+          g.pending.push_back(j);
         }
       }
-      if (j.gpu >= 0 && probes.count(j.gpu)) start(j);
-      for (auto &kv : probes) harvest(kv.first, false);
+      for (auto &kv : gpus) harvest(kv.first, kv.second, false);
+      for (auto &kv : gpus) start_grants(kv.first, kv.second);
       if (health_interval > 0 && time(nullptr) - last >= health_interval) {
         last = time(nullptr);
-        health_sweep();
+        for (auto &kv : gpus) start_health(kv.first, kv.second);
       }
     }
-    for (auto &kv : probes) {
-      harvest(kv.first, true);
-      if (arenas.count(kv.first)) gs_probe_mem_free(kv.second, arenas[kv.first]);
-      gs_probe_close(kv.second);
+    for (auto &kv : gpus) {
+      Gpu &g = kv.second;
+      harvest(kv.first, g, true);
+      if (g.sentinel) gs_probe_mem_free(g.probe, g.sentinel);
+      gs_probe_close(g.probe);
     }
   }
   void push(const ProbeJob &j) {
@@ -357,7 +487,8 @@ struct PluginInstance {
         probes->health_interval = f.health_check ? f.health_probe_interval : 0;
         for (const gs_gpu_info &g : mapped) {
           gs_probe *p = nullptr;
-          if (g.cuda_ordinal >= 0 && gs_probe_open(g.cuda_ordinal, &p) == GS_OK) probes->probes[g.nvml_index] = p;
+          if (g.cuda_ordinal >= 0 && gs_probe_open(g.cuda_ordinal, &p) == GS_OK)
+            probes->add_gpu(g.nvml_index, g.cuda_ordinal, g.total_bytes, p);
         }
       } else {
         logv(1, "probe disabled: %s", gs_cuda_last_error());
@@ -423,7 +554,7 @@ struct PluginInstance {
       }
     }
     *resp_len = res.resp_len;
-    if (rc == GS_OK && res.kind == GS_ALLOC_MATCHED && probes && probes->probes.count(res.gpu_index))
+    if (rc == GS_OK && res.kind == GS_ALLOC_MATCHED && probes && probes->gpus.count(res.gpu_index))
       probes->push(ProbeJob{res.gpu_index, res.pod_req_units * unit_bytes, res.pod_index});
     return rc;
   }
@@ -466,11 +597,24 @@ struct PluginInstance {
             gs_plugin_notify_health(plugin);
           }
         health_thread = std::thread([this] {
+          bool complained = false;
           while (!stop.load()) {
             gs_health_event ev;
-            if (gs_health_wait(1000, &ev) == GS_OK && !ev.ignored) {
+            const int rc = gs_health_wait(1000, &ev);
+            if (rc == GS_OK && !ev.ignored) {
               gs_law_mark_unhealthy_gpu(table, ev.gpu_index);
               gs_plugin_notify_health(plugin);
+            } else if (rc != GS_OK && rc != GS_E_TIMEOUT) {
+              // the event wait itself fails (GPU lost, driver reload): that is not a quiet second.
+              // Say so once, treat it as an event without a device (every GPU unhealthy, as
+              // nvidia.go:138-143 does for one), and do not spin on the error.
+              if (!complained) {
+                logv(0, "health watch: %s; marking all GPUs unhealthy", gs_nvml_last_error());
+                complained = true;
+                gs_law_mark_unhealthy_gpu(table, GS_ALL_GPUS);
+                gs_plugin_notify_health(plugin);
+              }
+              for (int i = 0; i < 10 && !stop.load(); ++i) usleep(100 * 1000);
             }
           }
         });
@@ -492,7 +636,7 @@ struct PluginInstance {
       probes->cv.notify_all();
       if (probes->th.joinable()) probes->th.join();
       else
-        for (auto &kv : probes->probes) gs_probe_close(kv.second);
+        for (auto &kv : probes->gpus) gs_probe_close(kv.second.probe);
       probes.reset();
     }
     if (plugin) gs_plugin_free(plugin);

@@ -76,6 +76,16 @@ class Probe:
     def free(self, dptr):
         L.check(self.lib.gs_probe_mem_free(self.h, C.c_void_p(dptr)), "gs_probe_mem_free")
 
+    def next_seed(self):
+        """A seed no earlier sweep of this engine used (gs_probe_next_seed)."""
+        v = C.c_uint32()
+        L.check(self.lib.gs_probe_next_seed(self.h, C.byref(v)), "gs_probe_next_seed")
+        return v.value
+
+    def test_skip_stores(self, on=True):
+        """Test hook: the store pass launches nothing while on."""
+        L.check(self.lib.gs_probe_test_skip_stores(self.h, int(on)), "gs_probe_test_skip_stores")
+
     def set_variant(self, write=-1, verify=-1, ctas_per_sm=-1):
         L.check(self.lib.gs_probe_set_variant(self.h, write, verify, ctas_per_sm),
                 "gs_probe_set_variant")
@@ -121,16 +131,21 @@ class Probe:
         self.submit(slices, passes)
         return self.wait()
 
-    def sweep_free(self, margin_bytes=2 << 30, seed=0x5EED):
-        """Health-time probe: sweep everything that is free right now minus a margin
-        (tenants' memory is theirs; only unallocated HBM can be written)."""
+    def sweep_free(self, margin_bytes=2 << 30, seed=None, pattern=L.GS_PROBE_PATTERN_HASH,
+                   max_bytes=None):
+        """Health-time probe: sweep what is free right now minus a margin, at most `max_bytes`
+        (tenants' memory is theirs; only unallocated HBM can be written). Every sweep gets a
+        seed of its own and, by default, the strong pattern."""
         free, _total = self.mem_info()
-        nbytes = (free - margin_bytes) & ~0xFFFFF
+        nbytes = free - margin_bytes
+        if max_bytes is not None:
+            nbytes = min(nbytes, max_bytes)
+        nbytes &= ~0xFFFFF
         if nbytes <= 0:
             return None, None
         d = self.alloc(nbytes)
         try:
-            verdicts, tm = self.run([(d, nbytes, seed)])
+            verdicts, tm = self.run([(d, nbytes, self.next_seed() if seed is None else seed, 0, pattern)])
         finally:
             self.free(d)
         return verdicts[0], tm
@@ -172,8 +187,10 @@ class ProbeScheduler:
     def __init__(self, probe: Probe, on_bad=None, max_pending=L.GS_PROBE_MAX_SLICES,
                  scrub_below=512 << 20):
         self.probe = probe
-        # batches containing a slice this small get an L2 scrub between the passes: without it
-        # the 126 MB L2 would serve (part of) the read-back instead of HBM
+        # a batch whose slices add up to less than this gets an L2 scrub between the passes:
+        # without it the 126 MB L2 would serve (part of) the read-back instead of HBM. What
+        # counts is the batch, not the slice: in a batch of many small slices the store pass
+        # itself has displaced a slice's lines long before the load pass comes back to it.
         self.scrub_below = scrub_below
         self.on_bad = on_bad
         self.max_pending = max_pending
@@ -190,17 +207,20 @@ class ProbeScheduler:
         self.scrub_ms = 0.0
         self.bad = 0
 
-    def grant(self, base, nbytes, seed, tag=0):
+    def grant(self, base, nbytes, seed=None, tag=0, pattern=L.GS_PROBE_PATTERN_LOWTOGGLE):
+        """Queue a granted range. seed None (the deployed form): the sweep that finally covers
+        the range draws a fresh seed from the engine, so no two sweeps of a range ever expect
+        the same data. A fixed seed is for tests that read the pattern back."""
         self.bytes_granted += nbytes
         for i, g in enumerate(self.pending):
             if g[0] == base:                      # same range granted again before it was
-                self.pending[i] = (base, nbytes, seed, tag)   # swept: one sweep covers both
+                self.pending[i] = (base, nbytes, seed, tag, pattern)   # swept: one sweep covers both
                 self.coalesced += 1
                 return
         if len(self.pending) >= self.max_pending:
             self.pending.pop(0)
             self.dropped += 1
-        self.pending.append((base, nbytes, seed, tag))
+        self.pending.append((base, nbytes, seed, tag, pattern))
 
     def _collect(self):
         verdicts, tm = self.probe.wait()
@@ -223,8 +243,10 @@ class ProbeScheduler:
             self._collect()
         if self.inflight is None and self.pending:
             batch, self.pending = self.pending, []
+            batch = [(b, n, self.probe.next_seed() if seed is None else seed, tag, pat)
+                     for b, n, seed, tag, pat in batch]
             passes = L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY
-            if min(s[1] for s in batch) < self.scrub_below:
+            if sum(s[1] for s in batch) < self.scrub_below:
                 passes |= L.GS_PROBE_SCRUB
             self.probe.submit(batch, passes)
             self.inflight = batch

@@ -428,6 +428,13 @@ GS_API int gs_probe_sm_count(const gs_probe *p, int *sms);
 GS_API int gs_probe_mem_alloc(gs_probe *p, uint64_t bytes, void **dptr);
 GS_API int gs_probe_mem_free(gs_probe *p, void *dptr);
 GS_API int gs_probe_mem_info(gs_probe *p, uint64_t *free_bytes, uint64_t *total_bytes);
+/* A seed no earlier sweep of this engine used: a nonce drawn when the engine was opened
+ * plus an odd multiple of a per-engine counter (2^32 sweeps before the first repeat). The
+ * pattern's only defence against a store pass that silently did nothing is that the data
+ * left by an earlier sweep never matches -- which holds only if every sweep gets a seed of
+ * its own; take it from here rather than from anything that can repeat (a pod index, a
+ * constant). One caller at a time, like the rest of a gs_probe.                        */
+GS_API int gs_probe_next_seed(gs_probe *p, uint32_t *seed);
 /* Asynchronous on the probe's stream. passes: bit0 = write, bit1 = verify, bit2 = scrub. */
 #define GS_PROBE_WRITE 1u
 #define GS_PROBE_VERIFY 2u
@@ -451,6 +458,11 @@ GS_API int gs_probe_run_granted(int cuda_ordinal, uint64_t bytes, uint32_t seed,
 /* Test hook: XOR `mask` into the 32-bit word at byte_offset of a slice. */
 GS_API int gs_probe_inject(gs_probe *p, void *base, uint64_t byte_offset,
                            uint32_t mask);
+/* Test hook: while on, the store pass of this engine launches nothing, as a store kernel that
+ * silently failed would. An engine opened with GS_PROBE_TEST_SKIP_STORES=n in the environment
+ * runs its first n-1 store passes and drops the rest (how the daemon's sweeps are put to the
+ * same test).                                                                               */
+GS_API int gs_probe_test_skip_stores(gs_probe *p, int on);
 /* Copy helpers so tests need no other CUDA binding. */
 GS_API int gs_probe_read(gs_probe *p, const void *dptr, void *host, uint64_t bytes);
 /* Kernel variant selection for tuning; -1 keeps the default.

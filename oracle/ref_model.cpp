@@ -613,6 +613,18 @@ REF_EXPORT int ref_allocate(void *h, const uint8_t *req, size_t len, int64_t now
   if (p->scratch.size() <= cap && resp) memcpy(resp, p->scratch.data(), p->scratch.size());
   return kind;
 }
+// The same call in the shape of gs_server_config.allocate (include/gpushare.h): bench.py serves
+// the reference model through the product's own transport for the matched over-the-socket leg
+// (user = the handle ref_new returned). 0, or -2 (GS_E_NOSPACE) with the required size.
+REF_EXPORT int ref_server_allocate(void *user, const uint8_t *req, size_t len, uint8_t *resp, size_t cap,
+                                   size_t *resp_len) {
+  RefPlugin *p = (RefPlugin *)user;
+  p->Allocate(req, len, 1, p->scratch);
+  *resp_len = p->scratch.size();
+  if (p->scratch.size() > cap) return -2;
+  memcpy(resp, p->scratch.data(), p->scratch.size());
+  return 0;
+}
 REF_EXPORT int ref_last_patched(void *h) { return ((RefPlugin *)h)->last_patched; }
 REF_EXPORT size_t ref_last_patch(void *h, char *buf, size_t cap) {
   RefPlugin *p = (RefPlugin *)h;

@@ -16,7 +16,6 @@ CORE_SO = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "libgpushare_
 
 DAEMON_BIN = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "gpushare-device-plugin-v2")
 INSPECT_BIN = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "kubectl-inspect-gpushare-v2")
-PODGETTER_BIN = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "podgetter")
 CSRC = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "csrc")
 HOST_SOURCES = ("allocate.cpp", "table.cpp", "gosem.cpp", "plugin.cpp", "errors.cpp", "grpc_server.cpp",
                 "grpc_client.cpp")
@@ -57,7 +56,7 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
     # Build once if the shared objects are missing (fresh checkout); never on the GPU box
     # if they travelled with the snapshot.
-    if not all(os.path.exists(p) for p in (FAKE_NVML, ORACLE_SO, CORE_SO, DAEMON_BIN, INSPECT_BIN, PODGETTER_BIN)):
+    if not all(os.path.exists(p) for p in (FAKE_NVML, ORACLE_SO, CORE_SO, DAEMON_BIN, INSPECT_BIN)):
         subprocess.run(["make", "-C", ROOT, "-j4"], check=True, stdout=subprocess.DEVNULL)
 
 

@@ -211,45 +211,3 @@ users: [{name: u, user: {token: abc}}]
     monkeypatch.delenv("KUBERNETES_SERVICE_HOST", raising=False)
     with pytest.raises(RuntimeError, match="in-cluster"):
         k8s_io.ApiConfig.load()
-
-
-def test_podgetter_prints_kubelet_pods(capsys):
-    from gpushare_b200 import podgetter
-    cluster = FakeCluster(PODS)
-    _Handler.cluster, _Handler.log = cluster, []
-    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), _Handler)
-    threading.Thread(target=srv.serve_forever, daemon=True).start()
-    try:
-        assert podgetter.main(["--token", "abc", "--kubelet-url", "http://127.0.0.1:%d" % srv.server_address[1]]) == 0
-    finally:
-        srv.shutdown()
-    out = json.loads(capsys.readouterr().out)
-    assert [p["metadata"]["name"] for p in out["items"]] == ["a", "b", "run", "other", "big"]
-    assert _Handler.log[0][3] == "Bearer abc"
-
-
-def test_native_podgetter_prints_kubelet_pods():
-    """bin/podgetter (daemon_cpp/podgetter_main.cpp): same flags, same request, the body as sent."""
-    import os
-    import subprocess
-
-    from tests.conftest import ROOT
-    exe = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "podgetter")
-    cluster = FakeCluster(PODS)
-    _Handler.cluster, _Handler.log = cluster, []
-    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), _Handler)
-    threading.Thread(target=srv.serve_forever, daemon=True).start()
-    try:
-        base = "http://127.0.0.1:%d" % srv.server_address[1]
-        out = subprocess.run([exe, "-token", "abc", "--kubelet-url=" + base, "-timeout", "5"],
-                             capture_output=True, text=True, timeout=30)
-    finally:
-        srv.shutdown()
-    assert out.returncode == 0
-    assert [p["metadata"]["name"] for p in json.loads(out.stdout)["items"]] == ["a", "b", "run", "other", "big"]
-    assert _Handler.log[0][3] == "Bearer abc"
-    out = subprocess.run([exe, "-token", "abc", "--kubelet-url=http://127.0.0.1:9"], capture_output=True,
-                         text=True, timeout=30)
-    assert out.returncode == 0 and "dial tcp 127.0.0.1:9" in out.stdout        # prints the error, returns
-    out = subprocess.run([exe, "--nope", "1"], capture_output=True, text=True, timeout=30)
-    assert out.returncode == 2 and "flag provided but not defined: -nope" in out.stderr

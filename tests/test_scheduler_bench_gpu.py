@@ -70,11 +70,56 @@ def test_colocation_tool_small_scale():
     assert len(r["probe"]["per_gpu"]) >= 1 and r["allocate"]["decisions"] == len(r["tenants_gib"])
 
 
-@pytest.mark.parametrize("program", ["python", "binary"])
-def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path, program):
-    """The daemon against the real NVML and GPU: enumerate, serve, Allocate for a pod bound to
-    GPU 0, sweep the granted range, and sweep free memory on the health timer."""
+def _start_daemon(tmp_path, pods, extra_env=None, interval=1):
+    import time
+    (tmp_path / "pods.json").write_text(json.dumps({"items": pods}))
+    env = dict(os.environ, NODE_NAME="node-a", PYTHONPATH=ROOT, **(extra_env or {}))
+    exe = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "gpushare-device-plugin-v2")
+    proc = subprocess.Popen([exe, "--v=1", "--memory-unit=GiB", "--socket-dir", str(tmp_path),
+                             "--pod-source-file", str(tmp_path / "pods.json"), "--no-register", "--probe",
+                             "--health-check", "--health-probe-interval=%d" % interval],
+                            env=env, stderr=subprocess.PIPE, text=True)
+    sock = str(tmp_path / "aliyungpushare.sock")
+    deadline = time.time() + 60
+    while not os.path.exists(sock) and time.time() < deadline:
+        time.sleep(0.1)
+    return proc, sock
+
+
+def _stop_daemon(proc):
     import signal
+    proc.send_signal(signal.SIGTERM)
+    try:
+        proc.wait(30)
+    except subprocess.TimeoutExpired:
+        proc.kill()
+    return proc.stderr.read()
+
+
+def _tenant(name, gib, assume):
+    return {"metadata": {"uid": "u-" + name, "name": name, "namespace": "default", "annotations": {
+        "ALIYUN_COM_GPU_MEM_IDX": "0", "ALIYUN_COM_GPU_MEM_ASSUME_TIME": str(assume),
+        "ALIYUN_COM_GPU_MEM_ASSIGNED": "false"}},
+        "spec": {"nodeName": "node-a", "containers": [
+            {"resources": {"limits": {"aliyun.com/gpu-mem": str(gib)}}}]}, "status": {"phase": "Pending"}}
+
+
+def _request(uuid, n):
+    ids = [(uuid + "-_-%d" % j).encode() for j in range(n)]
+    inner = b"".join(b"\x0a" + bytes([len(i)]) + i for i in ids)
+    ln = len(inner)
+    var = bytearray()
+    while ln >= 0x80:
+        var.append((ln & 0x7F) | 0x80)
+        ln >>= 7
+    var.append(ln)
+    return b"\x0a" + bytes(var) + inner
+
+
+def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
+    """The shipped daemon (the native binary) against the real NVML and GPU: enumerate, serve,
+    Allocate for pods bound to GPU 0, sweep the granted ranges -- grants that arrive while a sweep
+    is in flight share ONE launch pair -- and sweep free memory on the health timer."""
     import time
 
     import grpc
@@ -83,39 +128,82 @@ def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path, program
     from gpushare_b200.grpc_harness import KubeletStub
     with api.Nvml() as nv:
         uuid = nv.devices()[0].uuid.decode()
-    pods = {"items": [{"metadata": {"uid": "u1", "name": "tenant", "namespace": "default", "annotations": {
-        "ALIYUN_COM_GPU_MEM_IDX": "0", "ALIYUN_COM_GPU_MEM_ASSUME_TIME": "1",
-        "ALIYUN_COM_GPU_MEM_ASSIGNED": "false"}},
-        "spec": {"nodeName": "node-a", "containers": [
-            {"resources": {"limits": {"aliyun.com/gpu-mem": "2"}}}]}, "status": {"phase": "Pending"}}]}
-    (tmp_path / "pods.json").write_text(json.dumps(pods))
-    env = dict(os.environ, NODE_NAME="node-a", PYTHONPATH=ROOT)
-    exe = [sys.executable, "-m", "gpushare_b200.daemon"] if program == "python" else [
-        os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "gpushare-device-plugin-v2")]
-    proc = subprocess.Popen(exe + ["--v=1", "--memory-unit=GiB",
-                             "--socket-dir", str(tmp_path), "--pod-source-file", str(tmp_path / "pods.json"),
-                             "--no-register", "--probe", "--health-check", "--health-probe-interval=1"],
-                            env=env, stderr=subprocess.PIPE, text=True)
+    # a large tenant first: while its 80 GiB are being swept (~25 ms) the next two grants arrive
+    proc, sock = _start_daemon(tmp_path, [_tenant("big", 80, 1), _tenant("small-a", 2, 2), _tenant("small-b", 3, 3)])
     try:
-        sock = str(tmp_path / "aliyungpushare.sock")
-        deadline = time.time() + 60
-        while not os.path.exists(sock) and time.time() < deadline:
-            time.sleep(0.1)
         ch = KubeletStub.connect(sock)
         grpc.channel_ready_future(ch).result(timeout=30)
-        req = b"\x0a" + bytes([2 * (2 + len(uuid) + 4)]) + b"".join(
-            b"\x0a" + bytes([len(uuid) + 4]) + (uuid + "-_-%d" % j).encode() for j in (1, 2))
-        resp = KubeletStub.method(ch, "Allocate")(req)
-        assert b"ALIYUN_COM_GPU_MEM_IDX" in resp and b"no-gpu-has" not in resp
-        time.sleep(3.5)                                  # let the health timer fire
+        call = KubeletStub.method(ch, "Allocate")
+        for n in (80, 2, 3):
+            resp = call(_request(uuid, n))
+            assert b"ALIYUN_COM_GPU_MEM_IDX" in resp and b"no-gpu-has" not in resp
+        time.sleep(3.5)                                  # let the sweeps finish and the health timer fire
         ch.close()
     finally:
-        proc.send_signal(signal.SIGTERM)
-        try:
-            proc.wait(30)
-        except subprocess.TimeoutExpired:
-            proc.kill()
-    err = proc.stderr.read()
+        err = _stop_daemon(proc)
     assert proc.returncode == 0, err[-2000:]
-    assert "probe: gpu 0, 2147483648 bytes granted to pod 0 queued for a sweep" in err
+    assert "probe: gpu 0, %d bytes granted to pod 0 queued for a sweep" % (80 << 30) in err
+    assert "probe: gpu 0, 2 slice(s), %d bytes in one launch pair" % (5 << 30) in err, err[-3000:]
+    assert "in 2 slice(s), 2 launches" in err                       # one store pass, one load pass for both
     assert "health probe: gpu 0 swept" in err and "0 mismatching words" in err
+    assert "mismatching words" in err and " 0 mismatching words" in err
+    import re
+    assert all(int(m) == 0 for m in re.findall(r"(\d+) mismatching words", err)), err[-3000:]
+
+
+def test_daemon_health_sweep_catches_a_store_pass_that_did_nothing(tmp_path):
+    """Every sweep of the daemon draws a fresh seed, so a store kernel that silently does nothing
+    cannot hide behind what the previous sweep left in the same memory. Here the engine drops
+    every store pass after its second (the sentinel's and the first health sweep's run): the next
+    health sweep must find (nearly) every word wrong and the daemon must take the GPU out of
+    service. With one constant seed per sweep (as round 1 had it) that sweep read back clean."""
+    import re
+    import time
+
+    import grpc
+
+    from gpushare_b200.grpc_harness import KubeletStub
+    proc, sock = _start_daemon(tmp_path, [], {"GS_PROBE_TEST_SKIP_STORES": "3"})
+    try:
+        ch = KubeletStub.connect(sock)
+        grpc.channel_ready_future(ch).result(timeout=30)
+        time.sleep(4.5)                                  # at least three health ticks
+        stream = KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")
+        first = next(iter(stream))
+        stream.cancel()
+        ch.close()
+    finally:
+        err = _stop_daemon(proc)
+    assert proc.returncode == 0, err[-2000:]
+    sweeps = [(int(b), int(m)) for b, m in re.findall(r"health probe: gpu 0 swept (\d+) bytes .* (\d+) mismatching words", err)]
+    assert len(sweeps) >= 2, err[-3000:]
+    assert sweeps[0][1] == 0                              # stores ran: clean
+    assert sweeps[1][1] > 0.99 * (sweeps[1][0] // 16)     # stores dropped: the fresh seed exposes it
+    assert b"Unhealthy" in first and b"\x12\x07Healthy" not in first   # every device of the GPU went unhealthy
+
+
+def test_scheduler_sweep_catches_a_store_pass_that_did_nothing():
+    """The same property one level down, through the C ABI: ProbeScheduler sweeps a range, then the
+    store pass is disabled by the test hook and the SAME range is granted again. The second sweep
+    must report every word (its seed is new; the data is the first sweep's)."""
+    from gpushare_b200.probe import Probe, ProbeScheduler
+    bad = []
+    with Probe(0) as p:
+        arena = p.alloc(64 * MiB)
+        try:
+            s = ProbeScheduler(p, on_bad=lambda tag, v: bad.append((tag, v.mismatches)))
+            s.grant(arena, 64 * MiB, None, 5)
+            s.drain()
+            assert bad == [] and s.bytes_probed == 64 * MiB
+            p.test_skip_stores(True)
+            s.grant(arena, 64 * MiB, None, 5)
+            s.drain()
+            assert bad == [(5, 64 * MiB // 16)]
+            p.test_skip_stores(False)
+            s.grant(arena, 64 * MiB, None, 5)
+            s.drain()
+            assert len(bad) == 1                            # stores back: clean again
+            a, b = p.next_seed(), p.next_seed()
+            assert a != b
+        finally:
+            p.free(arena)

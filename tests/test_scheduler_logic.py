@@ -18,6 +18,12 @@ class FakeEngine:
     def idle(self):
         return not self.busy or self.finish_now
 
+    seeds = 1000
+
+    def next_seed(self):
+        self.seeds += 1
+        return self.seeds
+
     finish_now = False
 
     def wait(self):
@@ -74,13 +80,33 @@ def test_bad_verdicts_reach_the_callback():
     assert seen == [(7, 1)] and s.bad == 1
 
 
-def test_small_slices_get_an_l2_scrub():
+def test_small_batches_get_an_l2_scrub():
     e = FakeEngine()
     e.finish_now = True
     s = ProbeScheduler(e, scrub_below=1 << 20)
     s.grant(0, 4 << 20, 0, 0)
     s.drain()
-    s.grant(0, 4 << 20, 0, 0)
+    s.grant(0, 512 << 10, 0, 0)
     s.grant(0x1000000, 64 << 10, 0, 1)
     s.drain()
-    assert e.passes == [3, 7]            # write+verify; write+scrub+verify once a slice is below the bar
+    s.grant(0, 4 << 20, 0, 0)            # a small slice in a batch that is large enough as a whole
+    s.grant(0x1000000, 64 << 10, 0, 1)
+    s.drain()
+    assert e.passes == [3, 7, 3]         # write+verify; write+scrub+verify when the BATCH is below the bar
+
+
+def test_every_sweep_gets_a_seed_of_its_own():
+    """The deployed form of grant() passes no seed: each batch draws fresh ones from the engine,
+    so sweeping the same range twice never expects the same data (a store pass that did nothing
+    the second time would then be caught by the load pass)."""
+    e = FakeEngine()
+    e.finish_now = True
+    s = ProbeScheduler(e)
+    seen = []
+    for _wave in range(4):
+        s.grant(0x1000, 64, None, 0)
+        s.grant(0x2000, 64, None, 1, 1)
+        s.drain()
+        seen += [sl[2] for sl in e.submitted[-1]]
+        assert [sl[4] for sl in e.submitted[-1]] == [0, 1]       # the pattern travels with the grant
+    assert len(set(seen)) == len(seen) == 8
