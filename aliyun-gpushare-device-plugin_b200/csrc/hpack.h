@@ -6,12 +6,8 @@
 //
 // Decoder: complete for the representations of RFC 7541 section 6 (indexed, literal with /
 // without / never indexing, dynamic table size update), with the dynamic table. Huffman
-// strings (section 5.2, Appendix B) are decoded with the canonical form of the code: within
-// one code length the codes are consecutive in symbol order, so the table is rebuilt from
-// the per-length symbol lists. Only the lengths of NUL and the printable ASCII symbols
-// (5..15 bits) are carried here; every longer code starts with fifteen 1-bits and is
-// rejected as a compression error. gRPC header names and values are printable ASCII (binary
-// metadata is base64, grpc-message is percent-encoded), so kubelet never sends one.
+// strings (section 5.2, Appendix B) are decoded for all 256 byte values with the canonical
+// form of the code, rebuilt from the 257 code lengths.
 //
 // Encoder: what a gRPC endpoint needs -- static-table references and literals without
 // indexing, never Huffman -- so the peer's decoder keeps no state for us.
@@ -101,46 +97,60 @@ inline const StaticEntry *static_table() {
 }
 constexpr uint32_t kStaticCount = 61;
 
-// ---- Huffman (RFC 7541 Appendix B), canonical reconstruction ------------------------------
+// ---- Huffman (RFC 7541 Appendix B) ----------------------------------------------------------
+// The code of Appendix B is canonical: within one code length the codes are consecutive in symbol
+// order, and the first code of a length continues from the last code of the length before. The
+// 257 code LENGTHS therefore determine it (they add up to a complete code: sum of 2^-len == 1,
+// checked by tests/cpp/hpack_kat.cpp together with the RFC's own examples and a round trip of all
+// 256 byte values against nghttp2's decoder). All symbols decode, not only printable ASCII: a
+// peer may Huffman-code any header byte.
+constexpr int kHuffMaxLen = 30;
+constexpr int kHuffEos = 256;
 struct Huffman {
-  uint32_t first_code[16];  // first code of each length
-  uint16_t first_sym[16];   // index of that code's symbol in syms
-  uint8_t count[16];
-  uint8_t syms[96];
+  uint32_t first_code[kHuffMaxLen + 1];  // first code of each length
+  uint16_t first_sym[kHuffMaxLen + 1];   // index of that code's symbol in syms
+  uint16_t count[kHuffMaxLen + 1];
+  uint16_t syms[257];                    // symbols ordered by (length, value)
+  uint32_t code_of[257];                 // for the encoder side of tests
+  uint8_t len_of[257];
   Huffman() {
-    static const char *by_len[16] = {
-        nullptr, nullptr, nullptr, nullptr, nullptr,
-        "012aceiost",                          // 5 bits
-        " %-./3456789=A_bdfghlmnpru",          // 6
-        ":BCDEFGHIJKLMNOPQRSTUVWYjkqvwxyz",    // 7
-        "&*,;XZ",                              // 8
-        nullptr,                               // 9: none
-        "!\"()?",                              // 10
-        "'+|",                                 // 11
-        "#>",                                  // 12
-        nullptr,                               // 13: NUL $ @ [ ] ~ (NUL cannot sit in a literal)
-        "^}",                                  // 14
-        "<`{",                                 // 15
+    static const uint8_t lengths[257] = {
+      13, 23, 28, 28, 28, 28, 28, 28, 28, 24, 30, 28, 28, 30, 28, 28,  // 0..15
+      28, 28, 28, 28, 28, 28, 30, 28, 28, 28, 28, 28, 28, 28, 28, 28,  // 16..31
+       6, 10, 10, 12, 13,  6,  8, 11, 10, 10,  8, 11,  8,  6,  6,  6,  // 32..47
+       5,  5,  5,  6,  6,  6,  6,  6,  6,  6,  7,  8, 15,  6, 12, 10,  // 48..63
+      13,  6,  7,  7,  7,  7,  7,  7,  7,  7,  7,  7,  7,  7,  7,  7,  // 64..79
+       7,  7,  7,  7,  7,  7,  7,  7,  8,  7,  8, 13, 19, 13, 14,  6,  // 80..95
+      15,  5,  6,  5,  6,  5,  6,  6,  6,  5,  7,  7,  6,  6,  6,  5,  // 96..111
+       6,  7,  6,  5,  5,  6,  7,  7,  7,  7,  7, 15, 11, 14, 13, 28,  // 112..127
+      20, 22, 20, 20, 22, 22, 22, 23, 22, 23, 23, 23, 23, 23, 24, 23,  // 128..143
+      24, 24, 22, 23, 24, 23, 23, 23, 23, 21, 22, 23, 22, 23, 23, 24,  // 144..159
+      22, 21, 20, 22, 22, 23, 23, 21, 23, 22, 22, 24, 21, 22, 23, 23,  // 160..175
+      21, 21, 22, 21, 23, 22, 23, 23, 20, 22, 22, 22, 23, 22, 22, 23,  // 176..191
+      26, 26, 20, 19, 22, 23, 22, 25, 26, 26, 26, 27, 27, 26, 24, 25,  // 192..207
+      19, 21, 26, 27, 27, 26, 27, 24, 21, 21, 26, 26, 28, 27, 27, 27,  // 208..223
+      20, 24, 20, 21, 22, 21, 21, 23, 22, 22, 25, 25, 24, 24, 26, 23,  // 224..239
+      26, 27, 26, 26, 27, 27, 27, 27, 27, 28, 27, 27, 27, 27, 27, 26,  // 240..255
+      30,  // 256 = EOS
     };
     uint32_t code = 0;
     uint16_t k = 0;
-    for (int len = 1; len <= 15; ++len) {
+    first_code[0] = 0, first_sym[0] = 0, count[0] = 0;
+    for (int len = 1; len <= kHuffMaxLen; ++len) {
       code <<= 1;
       first_code[len] = code;
       first_sym[len] = k;
-      uint8_t n = 0;
-      if (len == 13) {
-        static const uint8_t l13[6] = {0, '$', '@', '[', ']', '~'};
-        for (uint8_t s : l13) syms[k++] = s, ++n;
-      } else if (by_len[len]) {
-        for (const char *p = by_len[len]; *p; ++p) syms[k++] = (uint8_t)*p, ++n;
-      }
+      uint16_t n = 0;
+      for (int sym = 0; sym < 257; ++sym)
+        if (lengths[sym] == len) {
+          syms[k++] = (uint16_t)sym;
+          code_of[sym] = code + n;
+          len_of[sym] = (uint8_t)len;
+          ++n;
+        }
       count[len] = n;
       code += n;
     }
-    first_code[0] = 0;
-    first_sym[0] = 0;
-    count[0] = 0;
   }
 };
 inline const Huffman &huffman() {
@@ -148,7 +158,8 @@ inline const Huffman &huffman() {
   return h;
 }
 
-// false: invalid padding, an EOS inside the string, or a symbol outside the carried set
+// false: padding that is not the leading bits of EOS or is 8 bits or longer, or an EOS inside the
+// string (RFC 7541 5.2: both are decoding errors)
 inline bool huffman_decode(const uint8_t *p, size_t n, std::string &out) {
   const Huffman &h = huffman();
   uint32_t code = 0;
@@ -161,17 +172,34 @@ inline bool huffman_decode(const uint8_t *p, size_t n, std::string &out) {
       if (len >= 5) {
         const uint32_t off = code - h.first_code[len];
         if (code >= h.first_code[len] && off < h.count[len]) {
-          out.push_back((char)h.syms[h.first_sym[len] + off]);
+          const uint16_t sym = h.syms[h.first_sym[len] + off];
+          if (sym == kHuffEos) return false;
+          out.push_back((char)(uint8_t)sym);
           code = 0;
           len = 0;
-        } else if (len == 15) {
-          return false;  // a 19..30-bit code (non-ASCII symbol or EOS)
+        } else if (len == kHuffMaxLen) {
+          return false;  // unreachable for a complete code; kept as a bound
         }
       }
     }
   }
-  // RFC 7541 5.2: padding is the most significant bits of EOS (all ones), fewer than 8
   return len <= 7 && code == ((1u << len) - 1u);
+}
+
+// Huffman-encode (the library's own encoder never does; tests and tools use it)
+inline void huffman_encode(const uint8_t *p, size_t n, std::vector<uint8_t> &out) {
+  const Huffman &h = huffman();
+  uint64_t acc = 0;
+  int bits = 0;
+  for (size_t i = 0; i < n; ++i) {
+    acc = (acc << h.len_of[p[i]]) | h.code_of[p[i]];
+    bits += h.len_of[p[i]];
+    while (bits >= 8) {
+      out.push_back((uint8_t)(acc >> (bits - 8)));
+      bits -= 8;
+    }
+  }
+  if (bits) out.push_back((uint8_t)((acc << (8 - bits)) | ((1u << (8 - bits)) - 1u)));
 }
 
 // ---- integers (RFC 7541 5.1) ---------------------------------------------------------------

@@ -210,8 +210,15 @@ inline bool http_request(const std::string &base_url, const std::string &method,
       err = detail::ssl_error();
       return false;
     }
-    const bool verify = !tls.insecure && (!tls.ca_file.empty() || !tls.ca_pem.empty());
+    // Verification is off only when the configuration says so (insecure-skip-tls-verify, or the
+    // kubelet client, main.go:41). A kubeconfig that names no CA is verified against the system's
+    // roots, as client-go does -- never silently left unauthenticated with a bearer token on it.
+    const bool verify = !tls.insecure;
     if (verify) {
+      if (tls.ca_file.empty() && tls.ca_pem.empty() && SSL_CTX_set_default_verify_paths(s.ctx) != 1) {
+        err = "unable to load the system's CA certificates: " + detail::ssl_error();
+        return false;
+      }
       if (!tls.ca_file.empty() && SSL_CTX_load_verify_locations(s.ctx, tls.ca_file.c_str(), nullptr) != 1) {
         err = "unable to load CA file " + tls.ca_file + ": " + detail::ssl_error();
         return false;

@@ -109,10 +109,12 @@ def _connection(url, timeout, ca_file=None, cert_file=None, key_file=None, insec
     u = urllib.parse.urlsplit(url)
     if u.scheme == "http":
         return http.client.HTTPConnection(u.hostname, u.port or 80, timeout=timeout), u
+    # verification is off only when the configuration says so (insecure-skip-tls-verify; the kubelet
+    # client, main.go:41); with no CA named, the system's roots apply, as in client-go
     have_ca = bool(ca_file or ca_data)
-    ctx = (ssl.create_default_context(cafile=ca_file, cadata=ca_data) if (have_ca and not insecure)
+    ctx = (ssl.create_default_context(cafile=ca_file, cadata=ca_data) if have_ca
            else ssl.create_default_context())
-    if insecure or not have_ca:
+    if insecure:
         ctx.check_hostname = False
         ctx.verify_mode = ssl.CERT_NONE
     if cert_file and key_file:

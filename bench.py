@@ -194,7 +194,9 @@ def pin_rank(local_rank, world):
     another rank): the Python loop, the library's serving thread of the over-socket leg and
     NCCL's helper threads of one rank then contend with nobody else's. The last core is left to
     the nvidia-smi sampler and whatever else the box runs. Returns a description for the line."""
+    global _BOX_CORES
     cores = physical_cores()
+    _BOX_CORES = len(cores)               # counted before the affinity mask shrinks the view
     usable = cores[:-1] if len(cores) > world else cores
     per = max(1, min(2, len(usable) // max(world, 1)))
     mine = usable[local_rank * per:(local_rank + 1) * per] or [usable[local_rank % len(usable)]]
@@ -268,6 +270,9 @@ def host_memcpy_gbps(n=256 << 20, reps=3):
     return best
 
 
+_BOX_CORES = None
+
+
 def host_info():
     model = ""
     try:
@@ -277,7 +282,8 @@ def host_info():
                 break
     except OSError:
         pass
-    return {"nproc": os.cpu_count(), "cpu": model, "physical_cores": len(physical_cores())}
+    return {"nproc": os.cpu_count(), "cpu": model,
+            "physical_cores": _BOX_CORES if _BOX_CORES is not None else len(physical_cores())}
 
 
 # ---------------------------------------------------------------- reference model -----

@@ -55,7 +55,11 @@ func buildTable(unit MemoryUnit) (*coreTable, error) {
 // The stream is registered with a raw codec (grpc.ForceServerCodec) whose Marshal returns
 // the []byte it is given.
 func (c *coreTable) listAndWatchBytes() []byte {
-	iov := make([]C.gs_iovec, int(C.gs_table_gpu_count(c.t)))
+	gpus := int(C.gs_table_gpu_count(c.t))
+	if gpus == 0 {
+		return nil // a node without GPUs advertises an empty list (an empty message)
+	}
+	iov := make([]C.gs_iovec, gpus)
 	var n C.uint32_t
 	C.gs_law_payload(c.t, &iov[0], C.uint32_t(len(iov)), &n)
 	out := make([]byte, 0, int(C.gs_law_payload_size(c.t)))
@@ -109,8 +113,22 @@ func (m *NvidiaDevicePlugin) allocateCore(req []byte, pods []v1.Pod, nowUnixNano
 	if len(views) > 0 {
 		vp = &views[0]
 	}
-	rc := C.gs_allocate(&ctx, (*C.uint8_t)(unsafe.SliceData(req)), C.size_t(len(req)), vp, C.size_t(len(views)),
-		(*C.uint8_t)(&resp[0]), C.size_t(len(resp)), (*C.char)(unsafe.Pointer(&patch[0])), C.size_t(len(patch)), &res)
+	call := func() C.int {
+		return C.gs_allocate(&ctx, (*C.uint8_t)(unsafe.SliceData(req)), C.size_t(len(req)), vp, C.size_t(len(views)),
+			(*C.uint8_t)(&resp[0]), C.size_t(len(resp)), (*C.char)(unsafe.Pointer(&patch[0])), C.size_t(len(patch)), &res)
+	}
+	rc := call()
+	if rc == C.GS_E_NOSPACE {
+		// a pod with many containers (about 230 bytes of response each): the required sizes came
+		// back in res; gs_allocate is stateless, so calling again decides the same thing
+		if int(res.resp_len) > len(resp) {
+			resp = make([]byte, int(res.resp_len))
+		}
+		if int(res.patch_len) > len(patch) {
+			patch = make([]byte, int(res.patch_len))
+		}
+		rc = call()
+	}
 	if rc != C.GS_OK {
 		return nil, nil, res, fmt.Errorf("gs_allocate: %s", C.GoString(C.gs_strerror(rc)))
 	}

@@ -105,6 +105,44 @@ int main() {
            "location: https://www.example.com\n",
            4, 222);
   }
+  {  // Appendix B as a whole: the lengths form a complete prefix code, EOS is thirty 1-bits, the
+     // codes the RFC prints for a few symbols come out of the canonical reconstruction
+    const Huffman &h = huffman();
+    unsigned long long kraft = 0;  // in units of 2^-30
+    for (int s = 0; s < 257; ++s) kraft += 1ull << (30 - h.len_of[s]);
+    bool ok = kraft == (1ull << 30) && h.len_of[256] == 30 && h.code_of[256] == 0x3fffffffu;
+    ok = ok && h.len_of['0'] == 5 && h.code_of['0'] == 0x0 && h.len_of['a'] == 5 && h.code_of['a'] == 0x3;
+    ok = ok && h.len_of[' '] == 6 && h.code_of[' '] == 0x14 && h.len_of[0] == 13 && h.code_of[0] == 0x1ff8;
+    ok = ok && h.len_of[1] == 23 && h.code_of[1] == 0x7fffd8 && h.len_of[255] == 26 && h.code_of[255] == 0x3ffffee;
+    ok = ok && h.len_of[10] == 30 && h.code_of[10] == 0x3ffffffc && h.len_of[22] == 30 && h.code_of[22] == 0x3ffffffe;
+    printf("%s Appendix B: complete code, EOS, spot codes\n", ok ? "ok  " : "FAIL");
+    failures += !ok;
+  }
+  {  // every byte value, Huffman-coded in one literal: a header block a peer may send
+    std::vector<uint8_t> all(256), enc, block;
+    for (int i = 0; i < 256; ++i) all[i] = (uint8_t)((i * 7 + 3) & 0xff);  // a permutation of 0..255
+    huffman_encode(all.data(), all.size(), enc);
+    block.push_back(0x00);  // literal without indexing, new name
+    encode_int(block, 0x00, 7, 5);
+    block.insert(block.end(), {'x', '-', 'b', 'i', 'n'});
+    encode_int(block, 0x80, 7, enc.size());  // H = 1
+    block.insert(block.end(), enc.begin(), enc.end());
+    Decoder d;
+    std::vector<Header> hs;
+    bool ok = d.decode(block.data(), block.size(), hs) && hs.size() == 1 && hs[0].name == "x-bin" &&
+              hs[0].value.size() == 256 && !memcmp(hs[0].value.data(), all.data(), 256);
+    printf("%s all 256 byte values Huffman-coded (%zu bytes)\n", ok ? "ok  " : "FAIL", enc.size());
+    failures += !ok;
+    printf("block ");
+    for (uint8_t b : block) printf("%02x", b);
+    printf("\n");
+    // an EOS inside a string and 8 bits of padding are decoding errors (RFC 7541 5.2)
+    const uint8_t eos_inside[] = {0x00, 0x01, 'x', 0x85, 0xff, 0xff, 0xff, 0xff, 0xff};   // 30 ones + more
+    const uint8_t long_pad[] = {0x00, 0x01, 'x', 0x82, 0x07, 0xff};                        // '0' + 3 pad, then 8 more
+    ok = !d.decode(eos_inside, sizeof eos_inside, hs) && !d.decode(long_pad, sizeof long_pad, hs);
+    printf("%s EOS inside a string / over-long padding rejected\n", ok ? "ok  " : "FAIL");
+    failures += !ok;
+  }
   {  // malformed input never reads out of bounds and is reported
     Decoder d;
     std::vector<Header> hs;

@@ -237,6 +237,16 @@ def test_binary_over_tls():
         finally:
             rig.close()
     with tempfile.TemporaryDirectory(prefix="gsc") as d:
+        # a kubeconfig that names no CA at all is verified against the system's roots (client-go's
+        # behaviour), so a self-signed apiserver is refused rather than trusted by default
+        good = _self_signed(d, "server")
+        rig = Rig(d, {}, False, tls=good, ca_line="")
+        try:
+            assert rig.proc.wait(30) == 1
+            assert "certificate verify failed" in rig.proc.stderr.read()
+        finally:
+            rig.close()
+    with tempfile.TemporaryDirectory(prefix="gsc") as d:
         good = _self_signed(d, "server")
         rig = Rig(d, {}, False, tls=good, ca_line="    insecure-skip-tls-verify: true\n",
                   capacity={"aliyun.com/gpu-count": "8"})

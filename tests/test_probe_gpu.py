@@ -356,3 +356,24 @@ def test_write_rate_follows_the_board(probe):
     finally:
         probe.set_write_rate(7600)                               # the default: fixed
         probe.free(d)
+
+
+def test_failed_allocation_does_not_poison_the_next_sweep(probe):
+    """An allocation that cannot be satisfied is an everyday event on a GPU shared with tenants.
+    The failure must be reported once, by the call that failed, and not again by the launch
+    check of the next sweep on the same thread (the CUDA runtime keeps a failed call's error
+    until it is read)."""
+    with pytest.raises(L.GpushareError) as e:
+        probe.alloc(1 << 50)                              # a pebibyte: never available
+    assert e.value.status == L.GS_E_CUDA
+    d = probe.alloc(4 * MiB)
+    try:
+        v, tm = probe.run([(d, 4 * MiB, probe.next_seed())])
+        assert v[0].clean and tm.launches == 2
+        rc = probe.lib.gs_probe_verify_noalloc(99, None, probe._slices([(d, 4 * MiB, 1)]), 1,
+                                               (L.SliceResult * 1)())   # no such device
+        assert rc in (L.GS_E_CUDA, L.GS_E_INVAL)
+        v, tm = probe.run([(d, 4 * MiB, probe.next_seed())])
+        assert v[0].clean
+    finally:
+        probe.free(d)
