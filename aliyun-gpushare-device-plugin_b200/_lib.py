@@ -87,7 +87,7 @@ class ServerStats(C.Structure):
     _fields_ = [("connections", C.c_uint64), ("requests", C.c_uint64),
                 ("allocate_calls", C.c_uint64), ("law_messages", C.c_uint64),
                 ("protocol_errors", C.c_uint64), ("bytes_in", C.c_uint64),
-                ("bytes_out", C.c_uint64)]
+                ("bytes_out", C.c_uint64), ("recv_body_ns", C.c_uint64), ("allocate_ns", C.c_uint64)]
 
 
 _P = C.POINTER

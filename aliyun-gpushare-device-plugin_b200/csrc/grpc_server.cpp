@@ -38,6 +38,11 @@ using namespace gs_h2;
 
 namespace {
 
+inline uint64_t mono_ns() {
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
+}
 constexpr uint64_t kSendSlice = 4u << 20;  // bytes of a device list per turn of the serving loop
 constexpr size_t kMaxStreams = 128;  // advertised in our SETTINGS and enforced
 constexpr size_t kMaxConns = 64;     // kubelet opens one; a bound on descriptors and buffers
@@ -171,7 +176,7 @@ struct gs_server {
 
   // stats (read from other threads)
   std::atomic<uint64_t> n_connections{0}, n_requests{0}, n_allocate{0}, n_law_messages{0},
-      n_bytes_in{0}, n_bytes_out{0}, n_protocol_errors{0};
+      n_bytes_in{0}, n_bytes_out{0}, n_protocol_errors{0}, ns_recv_body{0}, ns_allocate{0};
 
   void run();
   void accept_one();
@@ -561,6 +566,7 @@ bool gs_server::on_request_complete(Conn &c, Stream &s) {
         return true;
       }
       int rc = GS_OK;
+      const uint64_t t0 = mono_ns();
       for (int attempt = 0; attempt < 4; ++attempt) {
         gs_alloc_result res;
         rc = gs_plugin_allocate(plugin, msg, mlen, resp.data(), resp.size(), &res);
@@ -569,6 +575,7 @@ bool gs_server::on_request_complete(Conn &c, Stream &s) {
         if (rc != GS_E_NOSPACE) break;
         resp.resize(out_len > resp.size() * 2 ? out_len : resp.size() * 2);
       }
+      ns_allocate.fetch_add(mono_ns() - t0, std::memory_order_relaxed);
       if (rc == GS_E_WIRE)  // what grpc-go answers when proto.Unmarshal of the request fails
         return send_error(c, s, kInternal, "grpc: error unmarshalling request: malformed AllocateRequest");
       if (rc != GS_OK) return send_error(c, s, kUnknownCode, std::string("Allocate: ") + gs_strerror(rc));
@@ -635,7 +642,9 @@ bool gs_server::handle_frame(Conn &c, const FrameHeader &h) {
           if (!(h.flags & kFlagEndStream)) w.send_rst(sid, kErrNo);
         } else {
           if (!s.req->reserve(s.req->n + len)) return false;
+          const uint64_t t0 = mono_ns();
           if (!w.read_into(s.req->p + s.req->n, len) || !w.skip(pad)) return false;
+          ns_recv_body.fetch_add(mono_ns() - t0, std::memory_order_relaxed);
           s.req->n += len;
           s.recv_unacked += h.length;
           if (h.flags & kFlagEndStream) {
@@ -1041,6 +1050,8 @@ int gs_server_get_stats(const gs_server *s, gs_server_stats *out) {
   out->protocol_errors = s->n_protocol_errors.load(std::memory_order_relaxed);
   out->bytes_in = s->n_bytes_in.load(std::memory_order_relaxed);    // of closed connections
   out->bytes_out = s->n_bytes_out.load(std::memory_order_relaxed);
+  out->recv_body_ns = s->ns_recv_body.load(std::memory_order_relaxed);
+  out->allocate_ns = s->ns_allocate.load(std::memory_order_relaxed);
   return GS_OK;
 }
 

@@ -778,7 +778,14 @@ def run_ours(args, rank, world, local_rank):
                                          "in the library on both ends; the client stands in for kubelet)",
                             "allocate_calls_served_rank0": int(sock_stats["allocate_calls"]),
                             "request_bytes_per_step": int(req_avg * TENANTS * WAVES_PER_STEP),
-                            "socket_gbps_per_rank": sock_decisions / world / r_sock["dt"] * req_avg / 1e9},
+                            "socket_gbps_per_rank": sock_decisions / world / r_sock["dt"] * req_avg / 1e9,
+                            "where_the_time_goes_rank0": {
+                                "per_request_us": r_sock["mine"] / (sock_steps * WAVES_PER_STEP * TENANTS) * 1e6,
+                                "server_recv_of_body_us": sock_stats["recv_body_ns"] / max(sock_stats["allocate_calls"], 1) / 1e3,
+                                "server_scan_decide_encode_us": sock_stats["allocate_ns"] / max(sock_stats["allocate_calls"], 1) / 1e3,
+                                "note": "the body is copied twice by the kernel (client send, server recv); "
+                                        "recv() of the body overlaps the client's send, the rest is the "
+                                        "decision and the round trip"}},
             "single_queue": single_queue,
             "gpu_launches": int(la[0]),
             "roofline": {"bound": "hbm", "achieved": live_gbps, "peak": peak, "unit": "GB/s",

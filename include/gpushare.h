@@ -332,6 +332,8 @@ typedef struct gs_server_config {
 typedef struct gs_server_stats {
   uint64_t connections, requests, allocate_calls, law_messages, protocol_errors;
   uint64_t bytes_in, bytes_out;   /* of connections already closed */
+  uint64_t recv_body_ns;          /* spent in recv() of request bodies (DATA frames)          */
+  uint64_t allocate_ns;           /* spent in the built-in Allocate: scan + decision + encode  */
 } gs_server_stats;
 /* Start (server.go:114-142): removes a stale socket, listens, serves, and dials
  * itself (5 s) before returning. GS_E_STATE: cannot bind; GS_E_TIMEOUT: the
