@@ -924,7 +924,8 @@ def run_single_queue(args, n_gpus, gpus, lib, api, L, Probe, ProbeScheduler, C):
 def probe_size_curve(probe, base, arena_bytes, L):
     """Probe rate against slice size: one slice alone, and 64 slices of that size in one batch
     (what the scheduler makes of many small grants). An L2 scrub is added when the batch is
-    smaller than 512 MiB, as the scheduler does, and counts as time."""
+    smaller than 512 MiB, as the scheduler does, and counts as time. Both passes, CUDA events,
+    median of five after two settling runs."""
     MiB = 1 << 20
     rows = []
     for nbytes in (16 * MiB, 64 * MiB, 256 * MiB, 1024 * MiB, 2048 * MiB, 8192 * MiB, 40960 * MiB):
@@ -937,15 +938,15 @@ def probe_size_curve(probe, base, arena_bytes, L):
             passes = L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY
             if count * nbytes < 512 * MiB:
                 passes |= L.GS_PROBE_SCRUB
-            best = None
-            for _ in range(4):
+            rates = []
+            for it in range(7):                 # two to settle, the median of five
                 sl = [(base + k * nbytes, nbytes, probe.next_seed(), k) for k in range(count)]
                 v, tm = probe.run(sl, passes)
                 if not all(x.clean for x in v):
                     raise RuntimeError("size curve: dirty slice")
-                g = tm.gbps()
-                best = g if best is None or g > best else best
-            row[label + "_gbps"] = best
+                if it >= 2:
+                    rates.append(tm.gbps())
+            row[label + "_gbps"] = statistics.median(rates)
         rows.append(row)
     return rows
 
