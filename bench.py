@@ -925,7 +925,7 @@ def probe_size_curve(probe, base, arena_bytes, L):
     """Probe rate against slice size: one slice alone, and 64 slices of that size in one batch
     (what the scheduler makes of many small grants). An L2 scrub is added when the batch is
     smaller than 512 MiB, as the scheduler does, and counts as time. Both passes, CUDA events,
-    median of five after two settling runs."""
+    each form repeated for 0.2 s, median of the second half."""
     MiB = 1 << 20
     rows = []
     for nbytes in (16 * MiB, 64 * MiB, 256 * MiB, 1024 * MiB, 2048 * MiB, 8192 * MiB, 40960 * MiB):
@@ -938,15 +938,14 @@ def probe_size_curve(probe, base, arena_bytes, L):
             passes = L.GS_PROBE_WRITE | L.GS_PROBE_VERIFY
             if count * nbytes < 512 * MiB:
                 passes |= L.GS_PROBE_SCRUB
-            rates = []
-            for it in range(7):                 # two to settle, the median of five
+            rates, t0 = [], time.perf_counter()
+            while len(rates) < 6 or time.perf_counter() - t0 < 0.2:    # long enough for the clocks to settle
                 sl = [(base + k * nbytes, nbytes, probe.next_seed(), k) for k in range(count)]
                 v, tm = probe.run(sl, passes)
                 if not all(x.clean for x in v):
                     raise RuntimeError("size curve: dirty slice")
-                if it >= 2:
-                    rates.append(tm.gbps())
-            row[label + "_gbps"] = statistics.median(rates)
+                rates.append(tm.gbps())
+            row[label + "_gbps"] = statistics.median(rates[len(rates) // 2:])
         rows.append(row)
     return rows
 
