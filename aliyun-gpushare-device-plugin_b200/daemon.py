@@ -41,6 +41,9 @@ from . import api
 from .grpc_harness import KUBELET_SOCKET, SERVER_SOCK, DevicePluginServer
 
 
+_GPU_MEMORY = 0          # nvidia.go:13
+
+
 def parse_args(argv=None):
     """The ten flags of cmd/nvidia/main.go:15-26 with the same defaults."""
     ap = argparse.ArgumentParser(prog="gpushare-device-plugin-v2", allow_abbrev=False)
@@ -147,7 +150,14 @@ class PluginInstance:
         self.a, self.nv = a, nv
         infos = nv.devices()
         self.infos = infos
-        self.table = api.DeviceTable.from_gpus(infos, unit)         # getDevices
+        # nvidia.go:12-15,67-69: gpuMemory is a process global, set once from the first GPU and kept
+        # across plugin restarts; a restart re-reads UUIDs, never the unit count
+        global _GPU_MEMORY
+        if _GPU_MEMORY == 0:
+            self.table = api.DeviceTable.from_gpus(infos, unit)     # getDevices
+            _GPU_MEMORY = self.table.units_per_gpu
+        else:
+            self.table = api.DeviceTable([i.uuid.decode() for i in infos], _GPU_MEMORY, unit)
         self.source = None
         if a.pod_source_file:
             self.plugin = api.NvidiaDevicePlugin(self.table, node)

@@ -442,9 +442,26 @@ struct PluginInstance {
         err = std::string("nvml: ") + gs_nvml_last_error();
         return false;
       }
-    if (gs_table_build_from_gpus(infos.data(), n, unit, &table) != GS_OK) {
-      err = "cannot build the device table";
-      return false;
+    // nvidia.go:12-15,67-69: gpuMemory is a process global, set once from the first GPU and kept
+    // across plugin restarts (SIGHUP, kubelet restart) -- a restart re-reads UUIDs, never the unit count.
+    static uint64_t g_gpu_memory = 0;
+    if (g_gpu_memory == 0) {
+      if (gs_table_build_from_gpus(infos.data(), n, unit, &table) != GS_OK) {
+        err = "cannot build the device table";
+        return false;
+      }
+      g_gpu_memory = gs_table_units_per_gpu(table);
+    } else {
+      std::vector<const char *> uu(n);
+      std::vector<uint32_t> ul(n);
+      for (uint32_t i = 0; i < n; ++i) {
+        uu[i] = infos[i].uuid;
+        ul[i] = (uint32_t)strlen(infos[i].uuid);
+      }
+      if (gs_table_build(uu.data(), ul.data(), n, g_gpu_memory, unit, &table) != GS_OK) {
+        err = "cannot build the device table";
+        return false;
+      }
     }
     socket_path = f.socket_dir + "/" GS_SERVER_SOCK_NAME;
     kubelet_socket = f.socket_dir + "/kubelet.sock";

@@ -6,6 +6,8 @@
  * Environment:
  *   FAKE_NVML_GPUS      number of GPUs (default 8)
  *   FAKE_NVML_MEM_MIB   total memory per GPU in MiB (default 16384)
+ *   FAKE_NVML_MEM_FILE  path of a file holding that number instead; read at every memory query, so a
+ *                       test can change what the GPUs report between two plugin restarts
  *   FAKE_NVML_NO_EVENTS comma list of GPU indices that answer NOT_SUPPORTED to
  *                       nvmlDeviceRegisterEvents
  *   FAKE_NVML_EVENT_FIFO path of a FIFO read for lines "<gpu_index_or_-1> <xid>": events for
@@ -44,6 +46,19 @@ static struct fake_dev g_devs[MAX_GPUS];
 static struct fake_set g_set;
 static int g_init = 0, g_n = 8;
 static unsigned long long g_mem_mib = 16384;
+static unsigned long long mem_mib_now(void) {
+  const char *path = getenv("FAKE_NVML_MEM_FILE");
+  if (path && *path) {
+    FILE *f = fopen(path, "r");
+    if (f) {
+      unsigned long long v = 0;
+      const int ok = fscanf(f, "%llu", &v) == 1;
+      fclose(f);
+      if (ok) return v;
+    }
+  }
+  return g_mem_mib;
+}
 static int g_no_events[MAX_GPUS];
 
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
@@ -133,7 +148,7 @@ EXPORT nvmlReturn_t nvmlDeviceGetUUID(nvmlDevice_t d, char *buf, unsigned int le
 EXPORT nvmlReturn_t nvmlDeviceGetMemoryInfo_v2(nvmlDevice_t d, nvmlMemory_v2_t *m) {
   (void)d;
   if (!g_init) return NVML_ERROR_UNINITIALIZED;
-  m->total = g_mem_mib << 20;
+  m->total = mem_mib_now() << 20;
   m->reserved = 0;
   m->free = m->total;
   m->used = 0;
@@ -142,7 +157,7 @@ EXPORT nvmlReturn_t nvmlDeviceGetMemoryInfo_v2(nvmlDevice_t d, nvmlMemory_v2_t *
 EXPORT nvmlReturn_t nvmlDeviceGetMemoryInfo(nvmlDevice_t d, nvmlMemory_t *m) {
   (void)d;
   if (!g_init) return NVML_ERROR_UNINITIALIZED;
-  m->total = g_mem_mib << 20;
+  m->total = mem_mib_now() << 20;
   m->free = m->total;
   m->used = 0;
   return NVML_SUCCESS;

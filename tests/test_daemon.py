@@ -88,7 +88,9 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, prog
         json.dump({"items": c["pods"]}, open(pods, "w"))
         kubelet = KubeletStub(os.path.join(d, "kubelet.sock"))
         kubelet.start()
-        env = dict(os.environ, NODE_NAME=c["node"], FAKE_NVML_GPUS="2", FAKE_NVML_MEM_MIB="4096",
+        memfile = os.path.join(d, "mem_mib")
+        open(memfile, "w").write("4096")
+        env = dict(os.environ, NODE_NAME=c["node"], FAKE_NVML_GPUS="2", FAKE_NVML_MEM_FILE=memfile,
                    PYTHONPATH=ROOT)
         proc = subprocess.Popen(PROGRAMS[program] + ["--v=1", "--nvml-lib", FAKE_NVML,
                                  "--socket-dir", d, "--pod-source-file", pods],
@@ -102,6 +104,10 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, prog
             kubelet2.start()
             assert kubelet2.wait_registered(15), "no re-registration after kubelet.sock was re-created"
             n_before = len(kubelet2.registered)
+            # H7: the unit count is a process global of the reference (nvidia.go:12-15,67-69), set from
+            # GPU 0 once and kept across restarts: GPUs that report twice the memory after the restart
+            # are still advertised with 4 units each
+            open(memfile, "w").write("8192")
             proc.send_signal(signal.SIGHUP)
             deadline = time.time() + 15
             while len(kubelet2.registered) == n_before and time.time() < deadline:
@@ -110,7 +116,7 @@ def test_supervisor_reregisters_on_kubelet_restart_and_sighup(golden_cases, prog
             ch = KubeletStub.connect(os.path.join(d, "aliyungpushare.sock"))
             grpc.channel_ready_future(ch).result(timeout=10)
             devs = R.decode_list_and_watch(next(KubeletStub.method(ch, "ListAndWatch", stream=True)(b"")))
-            assert len(devs) == 8                        # 2 GPUs x 4 GiB
+            assert len(devs) == 8                        # 2 GPUs x 4 GiB, as before the restart
             ch.close()
             kubelet2.stop()
         finally:
