@@ -429,7 +429,10 @@ class NvidiaDevicePlugin:
         L.check(self.lib.gs_plugin_get_pod(self.h, i, C.byref(v)), "gs_plugin_get_pod")
 
         def s(x):
-            return None if not x.p else C.string_at(x.p, x.n).decode()
+            # absent (NULL) and present-but-empty differ: an empty ASSUME_TIME annotation still
+            # makes a pod "assumed" (podutils.go:92-96 tests presence, not content)
+            addr = C.cast(C.byref(x), C.POINTER(C.c_void_p))[0]
+            return None if not addr else C.string_at(addr, x.n).decode()
 
         return Pod(s(v.uid) or "", s(v.ns) or "", s(v.name) or "", s(v.node_name) or "",
                    v.gpu_mem_limit, s(v.ann_idx), s(v.ann_assume_time), s(v.ann_assigned))

@@ -301,10 +301,7 @@ size_t encode_patch(char *buf, size_t cap, int64_t now_unix_nano) {
   return need;
 }
 
-struct Cand {
-  uint64_t time;
-  uint32_t pod;
-};
+using gs_internal::Cand;
 
 // scratch that grows to the largest pod list seen, then is reused: no allocation in
 // steady state
@@ -352,31 +349,24 @@ int gs_allocate(const gs_alloc_ctx *ctx, const uint8_t *req, size_t req_len,
                 const gs_pod_view *pods, size_t n_pods, uint8_t *resp, size_t resp_cap,
                 char *patch, size_t patch_cap, gs_alloc_result *out) {
   if (!ctx || !ctx->table || !out || (!req && req_len) || (!pods && n_pods)) return GS_E_INVAL;
-  const gs_table *t = ctx->table;
-  memset(out, 0, sizeof(*out));
-  out->pod_index = -1;
-  out->gpu_index = -1;
+  return gs_internal::allocate_with_candidates(ctx, req, req_len, pods, n_pods, nullptr, 0, resp, resp_cap,
+                                               patch, patch_cap, out);
+}
 
-  // allocate.go:55-57 -- podReqGPU = sum of len(req.DevicesIDs)
-  uint32_t counts[kMaxContainers];
-  Scan s;
-  int rc = scan_request(req, req_len, counts, kMaxContainers, &s);
-  if (rc != GS_OK) return rc;
-  if (s.n_containers > kMaxContainers) return GS_E_LIMIT;
-  const uint64_t pod_req = s.total;
-  out->n_containers = s.n_containers;
-  out->pod_req_units = pod_req;
+}  // extern "C"
 
+namespace gs_internal {
+
+void build_candidates(gs_str node_name, const gs_pod_view *pods, size_t n_pods, std::vector<Cand> &cands) {
   // podmanager.go:273-293 -- this node's pods, first occurrence per UID;
   // podmanager.go:306-311 -- keep the assumed-but-unassigned ones
-  std::vector<Cand> &cands = tl_cands;
   cands.clear();
   if (n_pods <= 16) {
     for (size_t i = 0; i < n_pods; ++i) {
-      if (!str_eq(pods[i].node_name, ctx->node_name)) continue;
+      if (!str_eq(pods[i].node_name, node_name)) continue;
       bool dup = false;
       for (size_t k = 0; k < i && !dup; ++k)
-        dup = str_eq(pods[k].node_name, ctx->node_name) && str_eq(pods[k].uid, pods[i].uid);
+        dup = str_eq(pods[k].node_name, node_name) && str_eq(pods[k].uid, pods[i].uid);
       if (dup || !is_assumed(pods[i])) continue;
       cands.push_back(Cand{assume_time(pods[i]), (uint32_t)i});
     }
@@ -386,7 +376,7 @@ int gs_allocate(const gs_alloc_ctx *ctx, const uint8_t *req, size_t req_len,
     tl_slots.assign(cap, UINT32_MAX);
     tl_hashes.resize(n_pods);
     for (size_t i = 0; i < n_pods; ++i) {
-      if (!str_eq(pods[i].node_name, ctx->node_name)) continue;
+      if (!str_eq(pods[i].node_name, node_name)) continue;
       const uint64_t h = hash_bytes(pods[i].uid.p, pods[i].uid.n);
       tl_hashes[i] = h;
       size_t k = (size_t)h & (cap - 1);
@@ -404,6 +394,32 @@ int gs_allocate(const gs_alloc_ctx *ctx, const uint8_t *req, size_t req_len,
       if (is_assumed(pods[i])) cands.push_back(Cand{assume_time(pods[i]), (uint32_t)i});
     }
   }
+}
+
+int allocate_with_candidates(const gs_alloc_ctx *ctx, const uint8_t *req, size_t req_len,
+                             const gs_pod_view *pods, size_t n_pods, const Cand *known, size_t n_known,
+                             uint8_t *resp, size_t resp_cap, char *patch, size_t patch_cap,
+                             gs_alloc_result *out) {
+  const gs_table *t = ctx->table;
+  memset(out, 0, sizeof(*out));
+  out->pod_index = -1;
+  out->gpu_index = -1;
+
+  // allocate.go:55-57 -- podReqGPU = sum of len(req.DevicesIDs)
+  uint32_t counts[kMaxContainers];
+  Scan s;
+  int rc = scan_request(req, req_len, counts, kMaxContainers, &s);
+  if (rc != GS_OK) return rc;
+  if (s.n_containers > kMaxContainers) return GS_E_LIMIT;
+  const uint64_t pod_req = s.total;
+  out->n_containers = s.n_containers;
+  out->pod_req_units = pod_req;
+
+  std::vector<Cand> &cands = tl_cands;
+  if (known)
+    cands.assign(known, known + n_known);  // the sort below works on a copy: the caller's order stays lister order
+  else
+    build_candidates(ctx->node_name, pods, n_pods, cands);
 
   // podmanager.go:326-347 -- sort.Sort with Less(i,j) = time[i] <= time[j]
   {
@@ -469,4 +485,4 @@ int gs_allocate(const gs_alloc_ctx *ctx, const uint8_t *req, size_t req_len,
   return w.ok() ? GS_OK : GS_E_NOSPACE;
 }
 
-}  // extern "C"
+}  // namespace gs_internal

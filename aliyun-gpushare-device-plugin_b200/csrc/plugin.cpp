@@ -57,6 +57,10 @@ struct gs_plugin {
   std::mutex mu;                             // sync.RWMutex, taken as in allocate.go:60
   std::vector<StoredPod> pods;               // stand-in for the lister
   std::vector<gs_pod_view> views;            // rebuilt only when pods change shape
+  // getCandidatePods over the installed list, in list order: built when the list is installed,
+  // one entry dropped each time a pod is claimed -- a decision then costs the sort of the pending
+  // pods and the match, not a pass over every pod of the node
+  std::vector<gs_internal::Cand> cands;
   int64_t fixed_clock = 0;                   // 0 = time.Now()
   std::mutex health_mu;
   std::condition_variable health_cv;         // m.health channel
@@ -147,6 +151,7 @@ int gs_plugin_set_pods(gs_plugin *p, const gs_pod_view *pods, size_t n) {
     assign(s.assigned, pods[i].ann_assigned);
   }
   for (size_t i = 0; i < n; ++i) p->refresh_view(i);
+  gs_internal::build_candidates(view(p->node_name), p->views.data(), n, p->cands);
   return GS_OK;
 }
 
@@ -179,10 +184,18 @@ int gs_plugin_allocate(gs_plugin *p, const uint8_t *req, size_t req_len, uint8_t
   ctx.disable_cgpu_isolation = p->disable_cgpu_isolation ? 1 : 0;
   ctx.now_unix_nano = p->fixed_clock ? p->fixed_clock : real_now_ns();
   char patch[192];
-  const int rc = gs_allocate(&ctx, req, req_len, p->views.data(), p->views.size(), resp,
-                             resp_cap, patch, sizeof(patch), out);
+  if ((!req && req_len) || !p->table) return GS_E_INVAL;
+  const int rc = gs_internal::allocate_with_candidates(&ctx, req, req_len, p->views.data(), p->views.size(),
+                                                       p->cands.data(), p->cands.size(), resp, resp_cap, patch,
+                                                       sizeof(patch), out);
   if (rc != GS_OK) return rc;
   if (out->kind == GS_ALLOC_MATCHED) {
+    // claimed: ASSIGNED becomes "true", so the pod leaves the candidates (podutils.go:78-119)
+    for (size_t i = 0; i < p->cands.size(); ++i)
+      if (p->cands[i].pod == (uint32_t)out->pod_index) {
+        p->cands.erase(p->cands.begin() + (long)i);
+        break;
+      }
     // the PATCH of allocate.go:136 applied to the in-memory store:
     // {"metadata":{"annotations":{ASSIGNED:"true", ASSUME_TIME:"<now>"}}}
     StoredPod &s = p->pods[(size_t)out->pod_index];

@@ -64,9 +64,12 @@ SEED = 20261106
 # ---------------------------------------------------------------- workload ------------
 def tenant_sizes_gib(rank):
     """BASELINE config 4 per-GPU share: 8 sizes uniform in 1..40 GiB, redrawn until they fit
-    one B200 (sum <= 160 GiB so the probed ranges fit beside the CUDA context)."""
+    one B200 (sum <= 160 GiB so the probed ranges fit beside the CUDA context). Every GPU gets
+    the SAME eight sizes (weak scaling: the work per GPU is fixed; only the ids, the UUID and the
+    pod names differ from shard to shard), so `rank` does not enter the draw."""
     import random
-    rng = random.Random(SEED + rank)
+    del rank
+    rng = random.Random(SEED)
     if SMALL:
         return rng.sample(range(1, 40), TENANTS)
     while True:
@@ -754,9 +757,7 @@ def run_ours(args, rank, world, local_rank):
         live_ms = la[4] + la[5]
         live_gbps = 2 * la[1] / (live_ms * 1e-3) / 1e9 if live_ms else 0.0
         req_avg = sum(len(w) for w in wires) / len(wires)
-        cfg = workload_config(sizes, WAVES_PER_STEP, req_avg)
-        cfg["probe_arena_bytes"] = arena_bytes
-        cfg["uuid_source"] = uuid_source
+        cfg = workload_config(sizes, WAVES_PER_STEP, req_avg)      # identical in both arms
         sock_decisions = sock_steps * WAVES_PER_STEP * TENANTS * world
         line = {
             "metric": "allocate_decisions_per_s", "value": decisions / r_abi["dt"], "unit": "decisions/s",
@@ -804,7 +805,8 @@ def run_ours(args, rank, world, local_rank):
                                               "TB/s on this pool; the load+compare pass runs at that rate",
                          "how": "sum of slice bytes x 2 / (CUDA-event write ms + verify ms) over every "
                                 "probe batch launched inside the timed region, on the probe's stream"},
-            "probe": {"batches": int(la[7]), "launches_per_rank": la[0] / world,
+            "uuid_source": uuid_source,
+            "probe": {"batches": int(la[7]), "launches_per_rank": la[0] / world, "arena_bytes": arena_bytes,
                       "bytes_probed": int(la[1]), "bytes_granted": int(la[2]),
                       "coverage": la[1] / la[2] if la[2] else 0, "grants_dropped": int(la[3]),
                       "bad_slices": int(la[6]), "seeds": "fresh per sweep (gs_probe_next_seed)",

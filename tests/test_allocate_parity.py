@@ -105,6 +105,25 @@ def test_random_sequences_match_oracle(n_pods, ties):
             assert patched == want_patched, (n_pods, trial, step)
 
 
+@pytest.mark.parametrize("n_pods,ties", [(5, True), (20, True), (64, True), (150, False)])
+def test_plugin_candidate_cache_equals_stateless_allocate(n_pods, ties):
+    """gs_plugin filters the installed list once (getCandidatePods) and drops a pod when it claims
+    it; gs_allocate filters the list it is handed on every call. Both must decide alike at every
+    step of a claim sequence -- same kind, same pod, same response bytes -- with duplicate UIDs,
+    other nodes' pods and assume-time ties (any n: the two paths sort the very same sequence)."""
+    rng = random.Random(977 + n_pods)
+    for trial in range(12):
+        c = _random_case(rng, n_pods, rng.choice([1, 2, 8]), rng.choice(["GiB", "MiB"]), ties)
+        table, plug = product_for_case(c)
+        for step in range(min(2 * n_pods + 3, 60)):
+            wire = R.encode_allocate_request(_random_request(rng, c["gpus"]))
+            pods_now = [plug.get_pod(i) for i in range(plug.pod_count())]
+            want = api.allocate(table, c["node"], wire, pods_now, c["clock"], c["cgpu_disable"])
+            got = plug.Allocate(wire)
+            assert (got.kind, got.pod_index, got.gpu_index, got.response) == \
+                (want.kind, want.pod_index, want.gpu_index, want.response), (n_pods, trial, step)
+
+
 def test_ties_above_12_agree_with_oracle_port():
     """n > 12 with equal assume times: product and oracle both follow the published
     pdqsort, so they agree with each other; agreement with real Go is unpinned (H2)."""
