@@ -57,7 +57,7 @@ UNITS_B200_MIB = 183359          # nvidia-smi / NVML total of a B200 in MiB
 TENANTS = 8                      # config 4: 64 tenants over 8 GPUs
 PODS_IN_LIST = 64                # per GPU
 SMALL = bool(os.environ.get("GS_BENCH_SMALL"))        # CPU tests: MiB-sized tenants, short steps
-WAVES_PER_STEP = 8 if SMALL else 512                  # 4096 decisions per step
+WAVES_PER_STEP = 8 if SMALL else 640                  # 5120 decisions per step: 20 steps > 2 s
 SEED = 20261106
 
 
