@@ -46,7 +46,7 @@ struct Flags {
   // additions (not in the reference)
   std::string pod_source_file, nvml_lib, socket_dir = "/var/lib/kubelet/device-plugins", transport = "native";
   bool probe = false, no_register = false;
-  long health_probe_interval = 0;
+  long health_probe_interval = 0, probe_gather_ms = 2;
 };
 
 int g_v = 0;
@@ -80,6 +80,7 @@ void print_usage() {
         "  -nvml-lib string\n    \tpath of libnvidia-ml\n"
         "  -pod-source-file string\n    \tJSON file with the node's pods (stands in for the lister)\n"
         "  -probe\n    \tsweep each granted slice on the GPU after Allocate\n"
+        "  -probe-gather-ms int\n    \twith -probe: wait this long for more grants before a GPU's batch is swept (default 2)\n"
         "  -socket-dir string\n    \tdevice-plugins directory (default \"/var/lib/kubelet/device-plugins\")\n",
         stderr);
 }
@@ -107,7 +108,8 @@ Flags parse_flags(int argc, char **argv) {
                                                {"nvml-lib", &f.nvml_lib}, {"socket-dir", &f.socket_dir},
                                                {"transport", &f.transport}};
   std::map<std::string, long *> ints = {{"kubelet-port", &f.kubelet_port}, {"timeout", &f.timeout}, {"v", &f.v},
-                                        {"health-probe-interval", &f.health_probe_interval}};
+                                        {"health-probe-interval", &f.health_probe_interval},
+                                        {"probe-gather-ms", &f.probe_gather_ms}};
   for (int i = 1; i < argc; ++i) {
     std::string a = argv[i];
     if (a.size() < 2 || a[0] != '-') break;  // first non-flag argument ends parsing
@@ -175,6 +177,7 @@ struct ProbeWorker {
     uint64_t total_bytes = 0;
     uint64_t granted_bytes = 0;          // handed to tenants through this plugin since it started
     std::deque<ProbeJob> pending;        // grants waiting for the engine
+    std::chrono::steady_clock::time_point first_pending;  // when the oldest of them arrived
     std::vector<void *> arenas;          // ranges of the batch in flight (returned when it ends)
     std::vector<int32_t> tags;
     bool inflight = false;
@@ -192,6 +195,7 @@ struct ProbeWorker {
   gs_table *table = nullptr;
   gs_plugin *plugin = nullptr;
   long health_interval = 0;
+  long gather_ms = 2;  // after the first grant of a batch arrives, wait this long for company
 
   void add_gpu(int nvml_index, int cuda_ordinal, uint64_t total_bytes, gs_probe *p) {
     Gpu &g = gpus[nvml_index];
@@ -232,6 +236,11 @@ struct ProbeWorker {
   // the grants queued for one GPU -> one batch -> one launch pair
   void start_grants(int idx, Gpu &g) {
     if (g.inflight || g.pending.empty()) return;
+    // a pod's containers and the pods of one scheduling burst arrive within milliseconds of each
+    // other: a short gather window turns them into one launch pair (nobody waits for the sweep)
+    if (g.pending.size() < GS_PROBE_MAX_SLICES &&
+        std::chrono::steady_clock::now() - g.first_pending < std::chrono::milliseconds(gather_ms))
+      return;
     gs_slice sl[GS_PROBE_MAX_SLICES];
     memset(sl, 0, sizeof(sl));
     uint32_t n = 0;
@@ -361,7 +370,7 @@ struct ProbeWorker {
     time_t last = time(nullptr);
     while (!stop.load()) {
       bool busy = false;
-      for (auto &kv : gpus) busy |= kv.second.inflight;
+      for (auto &kv : gpus) busy |= kv.second.inflight || !kv.second.pending.empty();
       {
         std::unique_lock<std::mutex> lk(mu);
         // while a sweep is in flight come back soon to collect it; otherwise sleep until a grant arrives
@@ -373,6 +382,7 @@ struct ProbeWorker {
           if (it == gpus.end()) continue;
           Gpu &g = it->second;
           g.granted_bytes += j.bytes;
+          if (g.pending.empty()) g.first_pending = std::chrono::steady_clock::now();
           if (g.pending.size() >= GS_PROBE_MAX_SLICES) {  // HBM cannot be swept as fast as it is granted:
             g.pending.pop_front();                        // the newest grants win, the rest are counted
             ++g.dropped;
@@ -502,6 +512,7 @@ struct PluginInstance {
         probes->table = table;
         probes->plugin = plugin;
         probes->health_interval = f.health_check ? f.health_probe_interval : 0;
+        probes->gather_ms = f.probe_gather_ms < 0 ? 0 : f.probe_gather_ms;
         for (const gs_gpu_info &g : mapped) {
           gs_probe *p = nullptr;
           if (g.cuda_ordinal >= 0 && gs_probe_open(g.cuda_ordinal, &p) == GS_OK)

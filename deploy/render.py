@@ -25,7 +25,8 @@ DIFFERENCES = [
     "granularity alone is 90 MB",
     "NVIDIA_VISIBLE_DEVICES=all and NVIDIA_DRIVER_CAPABILITIES=compute,utility so the probe can run "
     "(the reference needs `utility` only: it never touches CUDA)",
-    "optional args --health-check and --probe",
+    "optional args --health-check and --probe (the probe costs each GPU the plugin's CUDA context, about "
+    "0.5 GiB, and a 64 MiB resident sentinel range; it sweeps HBM that is free when it runs, never a tenant's)",
 ]
 
 

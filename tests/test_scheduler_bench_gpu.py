@@ -70,14 +70,14 @@ def test_colocation_tool_small_scale():
     assert len(r["probe"]["per_gpu"]) >= 1 and r["allocate"]["decisions"] == len(r["tenants_gib"])
 
 
-def _start_daemon(tmp_path, pods, extra_env=None, interval=1):
+def _start_daemon(tmp_path, pods, extra_env=None, interval=1, extra_args=()):
     import time
     (tmp_path / "pods.json").write_text(json.dumps({"items": pods}))
     env = dict(os.environ, NODE_NAME="node-a", PYTHONPATH=ROOT, **(extra_env or {}))
     exe = os.path.join(ROOT, "aliyun-gpushare-device-plugin_b200", "bin", "gpushare-device-plugin-v2")
     proc = subprocess.Popen([exe, "--v=1", "--memory-unit=GiB", "--socket-dir", str(tmp_path),
                              "--pod-source-file", str(tmp_path / "pods.json"), "--no-register", "--probe",
-                             "--health-check", "--health-probe-interval=%d" % interval],
+                             "--health-check", "--health-probe-interval=%d" % interval] + list(extra_args),
                             env=env, stderr=subprocess.PIPE, text=True)
     sock = str(tmp_path / "aliyungpushare.sock")
     deadline = time.time() + 60
@@ -118,8 +118,9 @@ def _request(uuid, n):
 
 def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
     """The shipped daemon (the native binary) against the real NVML and GPU: enumerate, serve,
-    Allocate for pods bound to GPU 0, sweep the granted ranges -- grants that arrive while a sweep
-    is in flight share ONE launch pair -- and sweep free memory on the health timer."""
+    Allocate for pods bound to GPU 0, sweep the granted ranges -- grants that arrive within the
+    gather window (stretched to 1.5 s here so the test does not depend on timing) share ONE launch
+    pair -- and sweep free memory on the health timer."""
     import time
 
     import grpc
@@ -128,8 +129,8 @@ def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
     from gpushare_b200.grpc_harness import KubeletStub
     with api.Nvml() as nv:
         uuid = nv.devices()[0].uuid.decode()
-    # a large tenant first: while its 80 GiB are being swept (~25 ms) the next two grants arrive
-    proc, sock = _start_daemon(tmp_path, [_tenant("big", 80, 1), _tenant("small-a", 2, 2), _tenant("small-b", 3, 3)])
+    proc, sock = _start_daemon(tmp_path, [_tenant("big", 80, 1), _tenant("small-a", 2, 2), _tenant("small-b", 3, 3)],
+                               interval=3, extra_args=["--probe-gather-ms=1500"])
     try:
         ch = KubeletStub.connect(sock)
         grpc.channel_ready_future(ch).result(timeout=30)
@@ -137,14 +138,14 @@ def test_daemon_on_real_gpu_probes_at_allocate_and_health_time(tmp_path):
         for n in (80, 2, 3):
             resp = call(_request(uuid, n))
             assert b"ALIYUN_COM_GPU_MEM_IDX" in resp and b"no-gpu-has" not in resp
-        time.sleep(3.5)                                  # let the sweeps finish and the health timer fire
+        time.sleep(5.5)                                  # the gather window, the sweep, then the health timer
         ch.close()
     finally:
         err = _stop_daemon(proc)
     assert proc.returncode == 0, err[-2000:]
     assert "probe: gpu 0, %d bytes granted to pod 0 queued for a sweep" % (80 << 30) in err
-    assert "probe: gpu 0, 2 slice(s), %d bytes in one launch pair" % (5 << 30) in err, err[-3000:]
-    assert "in 2 slice(s), 2 launches" in err                       # one store pass, one load pass for both
+    assert "probe: gpu 0, 3 slice(s), %d bytes in one launch pair" % (85 << 30) in err, err[-3000:]
+    assert "in 3 slice(s), 2 launches" in err                       # one store pass, one load pass for all three
     assert "health probe: gpu 0 swept" in err and "0 mismatching words" in err
     assert "mismatching words" in err and " 0 mismatching words" in err
     import re
