@@ -170,12 +170,15 @@ struct ProbeWorker {
   static constexpr uint64_t kGrantMargin = 1ull << 30;      // free HBM left alone when sweeping a grant
   static constexpr uint64_t kHealthMargin = 2ull << 30;     // ... when sweeping free memory
   static constexpr uint64_t kSentinelBytes = 64ull << 20;   // kept per GPU for the no-allocation read-back
+  static constexpr int kGrowWindowSeconds = 600;            // how long a fresh grant is held free for its tenant
 
   struct Gpu {
     gs_probe *probe = nullptr;
     int cuda_ordinal = -1;
     uint64_t total_bytes = 0;
-    uint64_t granted_bytes = 0;          // handed to tenants through this plugin since it started
+    // grants of the last kGrowWindow: a tenant that was just admitted may not have allocated its
+    // memory yet, and a health sweep must leave that much alone
+    std::deque<std::pair<std::chrono::steady_clock::time_point, uint64_t>> recent_grants;
     std::deque<ProbeJob> pending;        // grants waiting for the engine
     std::chrono::steady_clock::time_point first_pending;  // when the oldest of them arrived
     std::vector<void *> arenas;          // ranges of the batch in flight (returned when it ends)
@@ -249,7 +252,10 @@ struct ProbeWorker {
       const ProbeJob j = g.pending.front();
       g.pending.pop_front();
       uint64_t free_b = 0, total_b = 0;
-      if (gs_probe_mem_info(g.probe, &free_b, &total_b) != GS_OK) break;
+      if (gs_probe_mem_info(g.probe, &free_b, &total_b) != GS_OK) {
+        logv(1, "probe skipped: %s", gs_cuda_last_error());
+        continue;
+      }
       uint64_t bytes = j.bytes;  // exactly the granted range, capped by what is free right now
       const uint64_t room = free_b > kGrantMargin ? free_b - kGrantMargin : 0;
       if (bytes > room) bytes = room;
@@ -289,15 +295,19 @@ struct ProbeWorker {
     logv(1, "probe: gpu %d, %u slice(s), %llu bytes in one launch pair", idx, n, (unsigned long long)total);
   }
   // Health-time probe. What may be written is memory nobody was promised: free HBM minus a
-  // margin, and never more than the GPU's total minus what this plugin has granted (a tenant
-  // that has not yet grown into its grant must still find it). The sweep covers HBM that is free
-  // now -- not the pages a tenant will later get. Started on every idle GPU, collected by poll.
+  // margin and minus what this plugin granted in the last ten minutes (a tenant that has not yet
+  // grown into its grant must still find it). The sweep covers HBM that is free now -- not the
+  // pages a tenant will later get. Started on every idle GPU, collected by poll.
   void start_health(int idx, Gpu &g) {
     if (g.inflight || !g.pending.empty()) return;
     uint64_t free_b = 0, total_b = 0;
     if (gs_probe_mem_info(g.probe, &free_b, &total_b) != GS_OK) return;
-    const uint64_t unreserved = g.total_bytes > g.granted_bytes ? g.total_bytes - g.granted_bytes : 0;
-    uint64_t bytes = free_b < unreserved ? free_b : unreserved;
+    const auto now = std::chrono::steady_clock::now();
+    while (!g.recent_grants.empty() && now - g.recent_grants.front().first > std::chrono::seconds(kGrowWindowSeconds))
+      g.recent_grants.pop_front();
+    uint64_t promised = 0;
+    for (const auto &rg : g.recent_grants) promised += rg.second;
+    uint64_t bytes = free_b > promised ? free_b - promised : 0;
     bytes = bytes > kHealthMargin ? (bytes - kHealthMargin) & ~0xFFFFFull : 0;
     if (bytes < (1ull << 30)) {
       sentinel_check(idx, g);  // nothing left to sweep: read the resident range back, allocating nothing
@@ -381,7 +391,7 @@ struct ProbeWorker {
           auto it = gpus.find(j.gpu);
           if (it == gpus.end()) continue;
           Gpu &g = it->second;
-          g.granted_bytes += j.bytes;
+          g.recent_grants.emplace_back(std::chrono::steady_clock::now(), j.bytes);
           if (g.pending.empty()) g.first_pending = std::chrono::steady_clock::now();
           if (g.pending.size() >= GS_PROBE_MAX_SLICES) {  // HBM cannot be swept as fast as it is granted:
             g.pending.pop_front();                        // the newest grants win, the rest are counted
