@@ -202,13 +202,17 @@ def pin_rank(local_rank, world):
     _BOX_CORES = len(cores)               # counted before the affinity mask shrinks the view
     usable = cores[:-1] if len(cores) > world else cores
     per = max(1, min(2, len(usable) // max(world, 1)))
-    mine = usable[local_rank * per:(local_rank + 1) * per] or [usable[local_rank % len(usable)]]
+    # spread the ranks over the whole socket instead of packing them into its first cores: the
+    # request scan is memory traffic, and neighbours share mesh stops and L3 slices
+    stride = max(per, len(usable) // max(world, 1))
+    mine = usable[local_rank * stride:local_rank * stride + per] or [usable[local_rank % len(usable)]]
     cpus = sorted(c for core in mine for c in core)
     try:
         os.sched_setaffinity(0, cpus)
     except OSError:
         return {"pinned": False}
     return {"pinned": True, "cpus": cpus, "physical_cores_on_box": len(cores), "cores_per_rank": per,
+            "stride": stride,
             "spare_cpus": list(cores[-1]) if len(cores) > world else []}
 
 
