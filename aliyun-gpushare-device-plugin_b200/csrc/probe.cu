@@ -11,6 +11,7 @@
 #include <time.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "gpushare.h"
@@ -160,9 +161,9 @@ struct gs_probe {
 static uint32_t fresh_nonce() {
   struct timespec ts;
   clock_gettime(CLOCK_MONOTONIC, &ts);
-  static int salt;
+  static std::atomic<uint32_t> opened{0};  // engines may be opened from several threads at once
   uint64_t x = (uint64_t)ts.tv_nsec ^ ((uint64_t)ts.tv_sec << 30) ^ ((uint64_t)getpid() << 17) ^
-               (uint64_t)(uintptr_t)&salt ^ ((uint64_t)++salt << 48);
+               (uint64_t)(uintptr_t)&opened ^ ((uint64_t)(opened.fetch_add(1) + 1) << 48);
   x ^= x >> 33;
   x *= 0xFF51AFD7ED558CCDull;
   x ^= x >> 33;

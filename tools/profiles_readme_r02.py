@@ -70,13 +70,21 @@ to two cores of its own (`placement`); the probe is flat at every N.
 
 try:
     a1, a8 = load("r02a_bench_1gpu.json"), load("r02a_bench_8gpu.json")
+    b1, b8 = load("r02b_bench_1gpu.json"), load("r02b_bench_8gpu.json")
     md += """
-**Run-to-run spread of the 8-GPU efficiency.** The same set taken an hour earlier on another 8-GPU box
-(`r02a_bench_*gpu.json`, 4 096-decision steps, otherwise the same code path): %.0f / %.0f decisions/s at 1 / 8 GPUs,
-per-GPU efficiency **%.3f** at 8, each of the eight ranks scanning %.1f GB/s. Same pinning, same binary: the boxes are
-VMs (32 vCPUs, the host's other tenants invisible), and what differs between the two runs is exactly the host-side
-scan rate under load; the probe figures agree to 0.1 %%.
-""" % (a1["value"], a8["value"], a8["value"] / 8 / a1["value"], a8["host_roofline"]["request_bytes_gbps_per_rank"])
+**Run-to-run spread of the 8-GPU efficiency.** Three calls on 8-GPU boxes, same binary:
+
+| call | rank placement | 1 GPU | 8 GPUs | per-GPU efficiency | request bytes scanned per rank at 8 |
+|---|---|---:|---:|---:|---:|
+| `r02a_bench_*` (4 096-decision steps) | ranks packed on cores 0-15 | %.0f | %.0f | **%.3f** | %.1f GB/s |
+| `r02_bench_*` (the table above) | packed | %.0f | %.0f | **%.3f** | %.1f GB/s |
+| `r02b_bench_*` (the committed `bench.py`) | spread over the socket (stride 3) | %.0f | %.0f | **%.3f** | %.1f GB/s |
+
+The boxes are VMs (32 vCPUs, the host's other tenants invisible); what differs between the calls is exactly the
+host-side scan rate under load, the probe figures agree to 0.1 %%. `bench.py` now spreads the ranks over the socket.
+""" % (a1["value"], a8["value"], a8["value"] / 8 / a1["value"], a8["host_roofline"]["request_bytes_gbps_per_rank"],
+       o1["value"], o8["value"], o8["value"] / 8 / o1["value"], o8["host_roofline"]["request_bytes_gbps_per_rank"],
+       b1["value"], b8["value"], b8["value"] / 8 / b1["value"], b8["host_roofline"]["request_bytes_gbps_per_rank"])
 except OSError:
     pass
 
