@@ -13,7 +13,6 @@ reference's calls depend on.
 """
 import os
 import tempfile
-import threading
 from concurrent import futures
 
 import pytest
