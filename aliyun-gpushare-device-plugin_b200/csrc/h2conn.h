@@ -137,6 +137,7 @@ struct Wire {
   size_t rpos = 0, rend = 0;
   uint64_t bytes_in = 0, bytes_out = 0;
 
+  static constexpr size_t kReadAhead = 16 << 10;
   explicit Wire(size_t cap = 256 << 10) : rbuf(cap) {}
 
   size_t buffered() const { return rend - rpos; }
@@ -152,7 +153,14 @@ struct Wire {
       rpos = rend = 0;
     }
     while (buffered() < need) {
-      const ssize_t r = recv(fd, rbuf.data() + rend, rbuf.size() - rend, 0);
+      // read ahead, but not far: what is read here and turns out to be a DATA payload is copied a
+      // second time by read_into, while the payload's remainder goes straight to its destination.
+      // 16 KiB takes a small request whole in one syscall and costs a 2 MB one ~1 us of copying
+      // instead of the ~20 us a buffer-full (256 KiB) of its body did.
+      size_t room = rbuf.size() - rend;
+      const size_t want = need - buffered() > kReadAhead ? need - buffered() : kReadAhead;
+      if (room > want) room = want;
+      const ssize_t r = recv(fd, rbuf.data() + rend, room, 0);
       if (r > 0) {
         rend += (size_t)r;
         bytes_in += (uint64_t)r;
