@@ -34,7 +34,7 @@ bool parse_u64_digits(const char *s, size_t n, uint64_t *out, bool *overflow);
 
 namespace {
 
-constexpr uint32_t kMaxContainers = gs_internal::kScanMaxContainers;
+constexpr uint32_t kMaxContainers = 1024;
 
 struct Scan {
   uint32_t n_containers = 0;
@@ -396,85 +396,20 @@ void build_candidates(gs_str node_name, const gs_pod_view *pods, size_t n_pods, 
   }
 }
 
-void request_scan_feed(RequestScanCursor &c, const uint8_t *msg, size_t avail) {
-  while (c.ok) {
-    if (c.cend == 0) {  // between containers: tag 0x0A (field 1, LEN) + the container's length
-      if (c.pos >= avail) return;
-      if (msg[c.pos] != 0x0A) {
-        c.ok = false;  // another field: the ordinary scan knows what to do with it
-        return;
-      }
-      size_t i = c.pos + 1;
-      uint64_t v = 0;
-      int shift = 0;
-      bool done = false;
-      while (i < avail && shift < 63) {
-        const uint8_t b = msg[i++];
-        v |= (uint64_t)(b & 0x7f) << shift;
-        shift += 7;
-        if (!(b & 0x80)) {
-          done = true;
-          break;
-        }
-      }
-      if (!done) {
-        if (shift >= 63) c.ok = false;
-        return;  // the length has not arrived in full yet
-      }
-      if (v > (1ull << 40) || c.n_containers >= kScanMaxContainers) {
-        c.ok = false;
-        return;
-      }
-      c.pos = i;
-      c.cend = i + (size_t)v;
-      c.cur = 0;
-    }
-    while (c.pos < c.cend) {
-      if (c.pos + 2 > avail) return;  // the next id's header has not arrived yet
-      if (msg[c.pos] != 0x0A || msg[c.pos + 1] >= 0x80) {
-        c.ok = false;
-        return;
-      }
-      const size_t adv = 2u + msg[c.pos + 1];
-      if (c.pos + adv > c.cend) {
-        c.ok = false;  // malformed: the ordinary scan reports it
-        return;
-      }
-      c.pos += adv;  // the id's bytes are never read (H9): hopping over bytes still in flight is fine
-      ++c.cur;
-    }
-    c.counts[c.n_containers++] = c.cur;
-    c.total += c.cur;
-    c.cend = 0;
-  }
-}
-
-bool request_scan_finish(RequestScanCursor &c, const uint8_t *msg, size_t len) {
-  if (c.ok) request_scan_feed(c, msg, len);
-  return c.ok && c.cend == 0 && c.pos == len;
-}
-
 int allocate_with_candidates(const gs_alloc_ctx *ctx, const uint8_t *req, size_t req_len,
                              const gs_pod_view *pods, size_t n_pods, const Cand *known, size_t n_known,
                              uint8_t *resp, size_t resp_cap, char *patch, size_t patch_cap,
-                             gs_alloc_result *out, const RequestScanCursor *pre) {
+                             gs_alloc_result *out) {
   const gs_table *t = ctx->table;
   memset(out, 0, sizeof(*out));
   out->pod_index = -1;
   out->gpu_index = -1;
 
   // allocate.go:55-57 -- podReqGPU = sum of len(req.DevicesIDs)
-  uint32_t own_counts[kMaxContainers];
-  const uint32_t *counts = own_counts;
+  uint32_t counts[kMaxContainers];
   Scan s;
-  if (pre) {  // counted while the request was arriving
-    s.n_containers = pre->n_containers;
-    s.total = pre->total;
-    counts = pre->counts;
-  } else {
-    int rc = scan_request(req, req_len, own_counts, kMaxContainers, &s);
-    if (rc != GS_OK) return rc;
-  }
+  int rc = scan_request(req, req_len, counts, kMaxContainers, &s);
+  if (rc != GS_OK) return rc;
   if (s.n_containers > kMaxContainers) return GS_E_LIMIT;
   const uint64_t pod_req = s.total;
   out->n_containers = s.n_containers;

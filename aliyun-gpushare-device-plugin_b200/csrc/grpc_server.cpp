@@ -43,7 +43,6 @@ inline uint64_t mono_ns() {
   clock_gettime(CLOCK_MONOTONIC, &ts);
   return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
 }
-constexpr size_t kScanChunk = 64u << 10;  // piece of a large Allocate body between two feeds of the id scan
 constexpr uint64_t kSendSlice = 4u << 20;  // bytes of a device list per turn of the serving loop
 constexpr size_t kMaxStreams = 128;  // advertised in our SETTINGS and enforced
 constexpr size_t kMaxConns = 64;     // kubelet opens one; a bound on descriptors and buffers
@@ -90,8 +89,6 @@ struct Stream {
   std::string path;
   std::string encoding;        // grpc-encoding of the request, if any
   std::unique_ptr<Buf> req;
-  // Allocate answered by the built-in decision: the id scan runs while the body arrives
-  std::unique_ptr<gs_internal::RequestScanCursor> scan;
   bool bad_content_type = false;
   int64_t send_window = kDefaultWindow;
   uint32_t recv_unacked = 0;
@@ -570,14 +567,9 @@ bool gs_server::on_request_complete(Conn &c, Stream &s) {
       }
       int rc = GS_OK;
       const uint64_t t0 = mono_ns();
-      // the ids were counted while the body arrived, if it had the shape kubelet sends; if the
-      // cursor met anything else, or did not end exactly at the end, the ordinary scan decides
-      const bool prescanned = s.scan && gs_internal::request_scan_finish(*s.scan, msg, mlen);
       for (int attempt = 0; attempt < 4; ++attempt) {
         gs_alloc_result res;
-        rc = prescanned ? gs_internal::plugin_allocate_prescanned(plugin, msg, mlen, *s.scan, resp.data(),
-                                                                  resp.size(), &res)
-                        : gs_plugin_allocate(plugin, msg, mlen, resp.data(), resp.size(), &res);
+        rc = gs_plugin_allocate(plugin, msg, mlen, resp.data(), resp.size(), &res);
         out_len = res.resp_len;
         if (rc == GS_OK && decision_fn) decision_fn(user, &res);
         if (rc != GS_E_NOSPACE) break;
@@ -651,24 +643,9 @@ bool gs_server::handle_frame(Conn &c, const FrameHeader &h) {
         } else {
           if (!s.req->reserve(s.req->n + len)) return false;
           const uint64_t t0 = mono_ns();
-          if (s.method == kAllocate && !allocate_fn && len >= kScanChunk) {
-            // a large Allocate body: take it in pieces and count ids in what has arrived while the
-            // kernel is still receiving the rest -- the scan hides behind the socket copy
-            if (!s.scan && s.req->n == 0) s.scan.reset(new (std::nothrow) gs_internal::RequestScanCursor());
-            size_t left = len;
-            while (left) {
-              const size_t k = left < kScanChunk ? left : kScanChunk;
-              if (!w.read_into(s.req->p + s.req->n, k)) return false;
-              s.req->n += k;
-              left -= k;
-              if (s.scan && s.req->n > 5) gs_internal::request_scan_feed(*s.scan, s.req->p + 5, s.req->n - 5);
-            }
-            if (!w.skip(pad)) return false;
-          } else {
-            if (!w.read_into(s.req->p + s.req->n, len) || !w.skip(pad)) return false;
-            s.req->n += len;
-          }
+          if (!w.read_into(s.req->p + s.req->n, len) || !w.skip(pad)) return false;
           ns_recv_body.fetch_add(mono_ns() - t0, std::memory_order_relaxed);
+          s.req->n += len;
           s.recv_unacked += h.length;
           if (h.flags & kFlagEndStream) {
             if (!on_request_complete(c, s)) return false;

@@ -105,19 +105,6 @@ gs_table *plugin_table(gs_plugin *p) { return p->table; }
 }  // namespace gs_internal
 
 extern "C" {
-static int plugin_allocate_impl(gs_plugin *p, const uint8_t *req, size_t req_len, uint8_t *resp,
-                                size_t resp_cap, gs_alloc_result *out,
-                                const gs_internal::RequestScanCursor *scan);
-}
-namespace gs_internal {
-int plugin_allocate_prescanned(gs_plugin *p, const uint8_t *req, size_t req_len,
-                               const RequestScanCursor &scan, uint8_t *resp, size_t resp_cap,
-                               gs_alloc_result *out) {
-  return plugin_allocate_impl(p, req, req_len, resp, resp_cap, out, &scan);
-}
-}  // namespace gs_internal
-
-extern "C" {
 
 int gs_plugin_new(gs_table *table, const char *node_name, size_t node_len,
                   int32_t disable_cgpu_isolation, gs_plugin **out) {
@@ -187,9 +174,8 @@ int gs_plugin_set_clock(gs_plugin *p, int64_t fixed_unix_nano) {
   return GS_OK;
 }
 
-static int plugin_allocate_impl(gs_plugin *p, const uint8_t *req, size_t req_len, uint8_t *resp,
-                                size_t resp_cap, gs_alloc_result *out,
-                                const gs_internal::RequestScanCursor *scan) {
+int gs_plugin_allocate(gs_plugin *p, const uint8_t *req, size_t req_len, uint8_t *resp,
+                       size_t resp_cap, gs_alloc_result *out) {
   if (!p || !out) return GS_E_INVAL;
   std::lock_guard<std::mutex> lk(p->mu);  // allocate.go:60-61
   gs_alloc_ctx ctx;
@@ -201,7 +187,7 @@ static int plugin_allocate_impl(gs_plugin *p, const uint8_t *req, size_t req_len
   if ((!req && req_len) || !p->table) return GS_E_INVAL;
   const int rc = gs_internal::allocate_with_candidates(&ctx, req, req_len, p->views.data(), p->views.size(),
                                                        p->cands.data(), p->cands.size(), resp, resp_cap, patch,
-                                                       sizeof(patch), out, scan);
+                                                       sizeof(patch), out);
   if (rc != GS_OK) return rc;
   if (out->kind == GS_ALLOC_MATCHED) {
     // claimed: ASSIGNED becomes "true", so the pod leaves the candidates (podutils.go:78-119)
@@ -234,11 +220,6 @@ static int plugin_allocate_impl(gs_plugin *p, const uint8_t *req, size_t req_len
     p->refresh_view((size_t)out->pod_index);
   }
   return GS_OK;
-}
-
-int gs_plugin_allocate(gs_plugin *p, const uint8_t *req, size_t req_len, uint8_t *resp,
-                       size_t resp_cap, gs_alloc_result *out) {
-  return plugin_allocate_impl(p, req, req_len, resp, resp_cap, out, nullptr);
 }
 
 int gs_plugin_get_device_plugin_options(gs_plugin *p, uint8_t *resp, size_t cap, size_t *len) {

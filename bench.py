@@ -788,11 +788,9 @@ def run_ours(args, rank, world, local_rank):
                                 "per_request_us": r_sock["mine"] / (sock_steps * WAVES_PER_STEP * TENANTS) * 1e6,
                                 "server_recv_of_body_us": sock_stats["recv_body_ns"] / max(sock_stats["allocate_calls"], 1) / 1e3,
                                 "server_scan_decide_encode_us": sock_stats["allocate_ns"] / max(sock_stats["allocate_calls"], 1) / 1e3,
-                                "note": "the body is copied twice by the kernel (client send, server recv); the "
-                                        "server takes it in 64 KiB pieces and counts ids in what has arrived "
-                                        "while the rest is in flight, so server_recv_of_body includes the id "
-                                        "scan and what remains after the last byte is match + encode; the rest "
-                                        "is the round trip and the caller"}},
+                                "note": "the body is copied twice by the kernel (client send, server recv); "
+                                        "recv() of the body overlaps the client's send, the rest is the "
+                                        "decision and the round trip"}},
             "single_queue": single_queue,
             "gpu_launches": int(la[0]),
             "roofline": {"bound": "hbm", "achieved": live_gbps, "peak": peak, "unit": "GB/s",
