@@ -244,6 +244,91 @@ def test_native_both_sides_large_messages(sockdir):
         small.Stop()
 
 
+def test_large_and_oddly_shaped_requests_over_the_socket_answer_like_in_process(sockdir):
+    """Large Allocate bodies (64 KiB and up: several recv()s, the multi-chain id scan) over the
+    socket. Whatever the request looks like -- kubelet's shape, several containers, ids of 128+
+    bytes, foreign fields, a container that runs past the end, trailing junk -- the answer must be
+    the one the in-process call gives on the same bytes: same envs and claim, or the same refusal."""
+    import random
+    uuid = "GPU-0f9b9cf4-2b1c-4a3e-9c1d-5e2f6a7b8c9d"
+    units = 183359
+    rng = random.Random(64)
+
+    def pod(k, units_):
+        return {"metadata": {"uid": "u%d" % k, "namespace": "default", "name": "t%d" % k, "annotations": {
+            "ALIYUN_COM_GPU_MEM_IDX": "0", "ALIYUN_COM_GPU_MEM_ASSUME_TIME": str(1000 + k),
+            "ALIYUN_COM_GPU_MEM_ASSIGNED": "false"}},
+            "spec": {"nodeName": "node-a", "containers": [{"name": "c", "resources": {"limits": {
+                "aliyun.com/gpu-mem": str(units_)}}}]}, "status": {"phase": "Pending"}}
+
+    def ids(n, width=0):
+        return [("%s-_-%d" % (uuid, rng.randrange(units))).ljust(width, "x") for _ in range(n)]
+
+    def varint(n):
+        out = bytearray()
+        while n >= 0x80:
+            out.append((n & 0x7F) | 0x80)
+            n >>= 7
+        out.append(n)
+        return bytes(out)
+
+    cases = []                                            # (name, wire)
+    cases.append(("one container, 3000 ids", R.encode_allocate_request([ids(3000)])))
+    cases.append(("exactly one piece", None))             # filled below: body of exactly 64 KiB
+    cases.append(("three containers", R.encode_allocate_request([ids(2000), ids(1), ids(4096)])))
+    cases.append(("empty container between", R.encode_allocate_request([ids(1500), [], ids(1500)])))
+    cases.append(("ids of 130 bytes", R.encode_allocate_request([ids(1200, 130)])))
+    cases.append(("one long id among short", R.encode_allocate_request([ids(1000) + ids(1, 300) + ids(1000)])))
+    base = R.encode_allocate_request([ids(2500)])
+    cases.append(("foreign varint field after", base + b"\x10\x07"))
+    cases.append(("foreign bytes field before", b"\x12\x03abc" + base))
+    cases.append(("trailing junk", base + b"\xff"))
+    cases.append(("container runs past the end", b"\x0a" + varint(len(base) + 10) + base[1 + len(varint(len(base) - 1 - len(varint(len(base))))):]))
+    inner = b"".join(b"\x0a" + bytes([len(i)]) + i.encode() for i in ids(2000))
+    cases.append(("foreign field inside a container", b"\x0a" + varint(len(inner) + 2) + inner[:50000] + b"\x18\x01" + inner[50000:]))
+    cases.append(("id length runs past its container", b"\x0a" + varint(len(inner)) + inner[:-1] + b"\x7f"))
+    cases.append(("non-canonical container length", b"\x0a" + varint(len(inner))[:-1] + bytes([varint(len(inner))[-1] | 0x80, 0x00]) + inner))
+    # a body of exactly 64 KiB with the 5-byte gRPC prefix: 1 258 records of 52 bytes and
+    # one of 111 make 65 527 bytes of ids, + tag + 3-byte length = 65 531
+    n_ids = 1259
+    body = R.encode_allocate_request([ids(1258, 50) + ids(1, 109)])
+    assert len(body) + 5 == 65536
+    cases[1] = ("exactly one piece", body)
+
+    table = api.DeviceTable([uuid], units, api.MiB)
+    outcomes = []
+    for name, wire in cases:
+        assert len(wire) + 5 >= 65536, name               # a large body
+        twin_pods = [api.Pod.from_k8s(pod(k, u)) for k, u in enumerate((3000, 6097, 1200, 2001, 1300, 2500, n_ids))]
+        served, local = api.NvidiaDevicePlugin(table, "node-a"), api.NvidiaDevicePlugin(table, "node-a")
+        served.set_clock(9)
+        local.set_clock(9)
+        served.set_pods(twin_pods)
+        local.set_pods(twin_pods)
+        srv = NativeDevicePluginServer(served, os.path.join(sockdir, "s.sock"))
+        srv.Start()
+        try:
+            with NativeClient(srv.socket) as cl:
+                try:
+                    got = ("ok", cl.call("Allocate", wire))
+                except RpcError as e:
+                    got = ("status", e.code)
+            try:
+                d = local.Allocate(wire)
+                want = ("ok", d.response)
+            except L.GpushareError as e:
+                want = ("status", 13 if e.status == L.GS_E_WIRE else 2)
+            assert got == want, name
+            assert [served.get_pod(i).ann_assigned for i in range(7)] == \
+                [local.get_pod(i).ann_assigned for i in range(7)], name
+            outcomes.append((name, got[0], "true" in [served.get_pod(i).ann_assigned for i in range(7)]))
+        finally:
+            srv.Stop()
+    claimed = [n for n, kind, took in outcomes if kind == "ok" and took]
+    refused = [n for n, kind, _t in outcomes if kind == "status"]
+    assert len(claimed) >= 7 and len(refused) >= 3, outcomes   # both kinds of answer were exercised
+
+
 def test_python_allocate_behind_native_server(golden_cases, sockdir):
     """A plugin whose Allocate is Python (the cluster plugin, the daemon's probe hook) is
     called back with the request bytes; its failures become statuses, not dead connections."""
