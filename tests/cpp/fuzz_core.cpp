@@ -48,6 +48,7 @@ static std::vector<uint8_t> rand_request() {
 }
 
 int main() {
+  long compared = 0;
   // Go-semantics helpers on arbitrary strings
   for (int i = 0; i < 50000; ++i) {
     const std::string s = rand_str("0123456789+-.eEinumkKMGTP _x", 40);
@@ -94,7 +95,8 @@ int main() {
     }
     // decisions over random pods and random (often malformed) requests
     gs_plugin *plug = nullptr;
-    gs_plugin_new(tab, "node-a", 6, (int)R(2), &plug);
+    const int32_t plugin_cgpu = (int32_t)R(2);
+    gs_plugin_new(tab, "node-a", 6, plugin_cgpu, &plug);
     for (int k = 0; k < 30; ++k) {
       const size_t np = R(R(5) ? 20 : 200);
       std::vector<std::string> keep;
@@ -120,8 +122,30 @@ int main() {
         const std::vector<uint8_t> req = rand_request();
         uint8_t resp[2048];
         gs_alloc_result res;
+        // what the stateless decision says about the plugin's pods as they are right now (after
+        // earlier claims): the plugin, which filters its list once and drops claimed pods, must
+        // answer the same -- kind, pod, GPU and response bytes
+        size_t cur_n = 0;
+        gs_plugin_pod_count(plug, &cur_n);
+        std::vector<gs_pod_view> cur(cur_n);
+        for (size_t i = 0; i < cur_n; ++i) gs_plugin_get_pod(plug, i, &cur[i]);
+        gs_plugin_set_clock(plug, 12345);
+        gs_alloc_ctx now_ctx{tab, gs_str{"node-a", 6}, plugin_cgpu, 12345};
+        uint8_t want_resp[2048];
+        char want_patch[192];
+        gs_alloc_result want;
+        const int want_rc = gs_allocate(&now_ctx, req.data(), req.size(), cur.data(), cur_n, want_resp,
+                                        sizeof want_resp, want_patch, sizeof want_patch, &want);
         const int rc = gs_plugin_allocate(plug, req.data(), req.size(), resp, sizeof resp, &res);
         if (rc == GS_OK && res.resp_len > sizeof resp) { printf("FAIL resp_len\n"); return 1; }
+        if (rc != want_rc || (rc == GS_OK && (res.kind != want.kind || res.pod_index != want.pod_index ||
+                                              res.gpu_index != want.gpu_index || res.resp_len != want.resp_len ||
+                                              memcmp(resp, want_resp, res.resp_len) != 0))) {
+          printf("FAIL plugin and stateless decision differ (rc %d/%d kind %d/%d pod %d/%d)\n", rc, want_rc,
+                 res.kind, want.kind, res.pod_index, want.pod_index);
+          return 1;
+        }
+        ++compared;
         char patch[8];  // deliberately too small: must report, not overrun
         gs_alloc_ctx ctx{tab, gs_str{"node-a", 6}, 0, (int64_t)rng()};
         uint8_t small[16];
@@ -131,6 +155,7 @@ int main() {
     gs_plugin_free(plug);
     gs_table_free(tab);
   }
+  printf("plugin vs stateless decisions compared: %ld\n", compared);
   printf("FUZZ CORE OK\n");
   return 0;
 }
