@@ -52,11 +52,15 @@ struct Flags {
 int g_v = 0;
 void logv(int level, const char *fmt, ...) {
   if (g_v < level) return;
+  char line[1024];
   va_list ap;
   va_start(ap, fmt);
-  vfprintf(stderr, fmt, ap);
+  int n = vsnprintf(line, sizeof(line) - 1, fmt, ap);
   va_end(ap);
-  fputc('\n', stderr);
+  if (n < 0) return;
+  if (n > (int)sizeof(line) - 2) n = (int)sizeof(line) - 2;
+  line[n] = '\n';
+  fwrite(line, 1, (size_t)n + 1, stderr);  // one write per line: the probe threads log too
   fflush(stderr);
 }
 
@@ -152,13 +156,14 @@ Flags parse_flags(int argc, char **argv) {
 }
 
 // ---- the slice probe beside Allocate (no counterpart in the reference) --------------------------
-// One worker thread owns every CUDA call and never waits for a sweep: a grant is queued when its
-// answer has left, the worker gathers what has queued up for a GPU into one batch (at most
-// GS_PROBE_MAX_SLICES slices per launch pair, an L2 scrub between the passes when the batch is
-// smaller than the L2 can hide), submits it and goes on; finished batches are collected by
-// polling. Health-time sweeps of free memory start on every idle GPU at once and are collected the
-// same way, so a node's sweep takes one GPU's time, not the sum. Every sweep draws its seeds from
-// the engine (gs_probe_next_seed): what an earlier sweep left in a range never matches.
+// One worker thread PER GPU owns every CUDA call for that GPU and never waits for a sweep: a grant
+// is queued when its answer has left, the worker gathers what has queued up into one batch (at
+// most GS_PROBE_MAX_SLICES slices per launch pair, an L2 scrub between the passes when the batch is
+// smaller than the L2 can hide), submits it and goes on; finished batches are collected by polling.
+// Health-time sweeps of free memory fire on every GPU at the same instant (the ticks are counted
+// from one shared epoch), each on its own thread -- allocation, sweep and release included -- so a
+// node's sweep takes one GPU's time, not the sum. Every sweep draws its seeds from the engine
+// (gs_probe_next_seed): what an earlier sweep left in a range never matches.
 struct ProbeJob {
   int gpu;
   uint64_t bytes;
@@ -171,41 +176,48 @@ struct ProbeWorker {
   static constexpr uint64_t kHealthMargin = 2ull << 30;     // ... when sweeping free memory
   static constexpr uint64_t kSentinelBytes = 64ull << 20;   // kept per GPU for the no-allocation read-back
   static constexpr int kGrowWindowSeconds = 600;            // how long a fresh grant is held free for its tenant
+  using Clock = std::chrono::steady_clock;
 
   struct Gpu {
+    int index = -1;  // NVML index
     gs_probe *probe = nullptr;
     int cuda_ordinal = -1;
     uint64_t total_bytes = 0;
     // grants of the last kGrowWindow: a tenant that was just admitted may not have allocated its
     // memory yet, and a health sweep must leave that much alone
-    std::deque<std::pair<std::chrono::steady_clock::time_point, uint64_t>> recent_grants;
+    std::deque<std::pair<Clock::time_point, uint64_t>> recent_grants;
     std::deque<ProbeJob> pending;        // grants waiting for the engine
-    std::chrono::steady_clock::time_point first_pending;  // when the oldest of them arrived
+    Clock::time_point first_pending;     // when the oldest of them arrived
     std::vector<void *> arenas;          // ranges of the batch in flight (returned when it ends)
     std::vector<int32_t> tags;
     bool inflight = false;
     bool inflight_is_health = false;
+    Clock::time_point health_tick;       // the tick the health sweep in flight belongs to
     void *sentinel = nullptr;            // written once at start, read back without allocating
     uint32_t sentinel_seed = 0;
     uint64_t dropped = 0;
+    std::mutex mu;                       // guards queue
+    std::condition_variable cv;
+    std::deque<ProbeJob> queue;          // from the Allocate path
+    std::thread th;
   };
-  std::map<int, Gpu> gpus;  // NVML index -> state
-  std::mutex mu;
-  std::condition_variable cv;
-  std::deque<ProbeJob> queue;
+  std::map<int, std::unique_ptr<Gpu>> gpus;  // NVML index -> state; the map itself is fixed once the threads run
   std::atomic<bool> stop{false};
-  std::thread th;
   gs_table *table = nullptr;
   gs_plugin *plugin = nullptr;
   long health_interval = 0;
   long gather_ms = 2;  // after the first grant of a batch arrives, wait this long for company
+  Clock::time_point epoch;
 
   void add_gpu(int nvml_index, int cuda_ordinal, uint64_t total_bytes, gs_probe *p) {
-    Gpu &g = gpus[nvml_index];
-    g.probe = p;
-    g.cuda_ordinal = cuda_ordinal;
-    g.total_bytes = total_bytes;
+    std::unique_ptr<Gpu> g(new Gpu());
+    g->index = nvml_index;
+    g->probe = p;
+    g->cuda_ordinal = cuda_ordinal;
+    g->total_bytes = total_bytes;
+    gpus[nvml_index] = std::move(g);
   }
+  bool has(int nvml_index) const { return gpus.count(nvml_index) != 0; }
   void mark_bad(int gpu) {
     gs_law_mark_unhealthy_gpu(table, gpu);
     gs_plugin_notify_health(plugin);
@@ -217,7 +229,7 @@ struct ProbeWorker {
     g.tags.clear();
     g.inflight = false;
   }
-  void harvest(int idx, Gpu &g, bool block) {
+  void harvest(Gpu &g, bool block) {
     if (!g.inflight) return;
     if (!block && gs_probe_poll(g.probe) != GS_OK) return;
     gs_slice_result r[GS_PROBE_MAX_SLICES];
@@ -228,21 +240,25 @@ struct ProbeWorker {
       unsigned long long bad = 0;
       for (size_t i = 0; i < g.arenas.size(); ++i) bad += r[i].mismatches;
       logv(1, "%s: gpu %d swept %llu bytes in %zu slice(s), %u launches, at %.0f GB/s, %llu mismatching words", label,
-           idx, (unsigned long long)tm.bytes, g.arenas.size(), tm.launches,
+           g.index, (unsigned long long)tm.bytes, g.arenas.size(), tm.launches,
            ms > 0 ? 2.0 * (double)tm.bytes / ms / 1e6 : 0.0, bad);
-      if (bad) mark_bad(idx);
+      if (bad) mark_bad(g.index);
     } else {
-      logv(1, "%s: gpu %d: %s", label, idx, gs_cuda_last_error());
+      logv(1, "%s: gpu %d: %s", label, g.index, gs_cuda_last_error());
     }
+    const bool was_health = g.inflight_is_health;
     release(g);
+    if (was_health)
+      logv(1, "health probe: gpu %d done %.0f ms after the tick (allocation, sweep and release)", g.index,
+           std::chrono::duration<double, std::milli>(Clock::now() - g.health_tick).count());
   }
   // the grants queued for one GPU -> one batch -> one launch pair
-  void start_grants(int idx, Gpu &g) {
+  void start_grants(Gpu &g) {
     if (g.inflight || g.pending.empty()) return;
     // a pod's containers and the pods of one scheduling burst arrive within milliseconds of each
     // other: a short gather window turns them into one launch pair (nobody waits for the sweep)
     if (g.pending.size() < GS_PROBE_MAX_SLICES &&
-        std::chrono::steady_clock::now() - g.first_pending < std::chrono::milliseconds(gather_ms))
+        Clock::now() - g.first_pending < std::chrono::milliseconds(gather_ms))
       return;
     gs_slice sl[GS_PROBE_MAX_SLICES];
     memset(sl, 0, sizeof(sl));
@@ -261,7 +277,7 @@ struct ProbeWorker {
       if (bytes > room) bytes = room;
       bytes &= ~0xFFFFFull;
       if (!bytes) {
-        logv(1, "probe skipped: gpu %d has no free memory left for the %llu bytes granted to pod %d", idx,
+        logv(1, "probe skipped: gpu %d has no free memory left for the %llu bytes granted to pod %d", g.index,
              (unsigned long long)j.bytes, j.pod_index);
         continue;
       }
@@ -278,7 +294,7 @@ struct ProbeWorker {
       sl[n].tag = (uint32_t)j.pod_index;
       sl[n].pattern = GS_PROBE_PATTERN_LOWTOGGLE;
       total += bytes;
-      logv(1, "probe: gpu %d, %llu bytes granted to pod %d queued for a sweep", idx, (unsigned long long)bytes,
+      logv(1, "probe: gpu %d, %llu bytes granted to pod %d queued for a sweep", g.index, (unsigned long long)bytes,
            j.pod_index);
       ++n;
     }
@@ -292,17 +308,17 @@ struct ProbeWorker {
     }
     g.inflight = true;
     g.inflight_is_health = false;
-    logv(1, "probe: gpu %d, %u slice(s), %llu bytes in one launch pair", idx, n, (unsigned long long)total);
+    logv(1, "probe: gpu %d, %u slice(s), %llu bytes in one launch pair", g.index, n, (unsigned long long)total);
   }
   // Health-time probe. What may be written is memory nobody was promised: free HBM minus a
   // margin and minus what this plugin granted in the last ten minutes (a tenant that has not yet
   // grown into its grant must still find it). The sweep covers HBM that is free now -- not the
-  // pages a tenant will later get. Started on every idle GPU, collected by poll.
-  void start_health(int idx, Gpu &g) {
+  // pages a tenant will later get.
+  void start_health(Gpu &g, Clock::time_point tick) {
     if (g.inflight || !g.pending.empty()) return;
     uint64_t free_b = 0, total_b = 0;
     if (gs_probe_mem_info(g.probe, &free_b, &total_b) != GS_OK) return;
-    const auto now = std::chrono::steady_clock::now();
+    const auto now = Clock::now();
     while (!g.recent_grants.empty() && now - g.recent_grants.front().first > std::chrono::seconds(kGrowWindowSeconds))
       g.recent_grants.pop_front();
     uint64_t promised = 0;
@@ -310,13 +326,13 @@ struct ProbeWorker {
     uint64_t bytes = free_b > promised ? free_b - promised : 0;
     bytes = bytes > kHealthMargin ? (bytes - kHealthMargin) & ~0xFFFFFull : 0;
     if (bytes < (1ull << 30)) {
-      sentinel_check(idx, g);  // nothing left to sweep: read the resident range back, allocating nothing
+      sentinel_check(g);  // nothing left to sweep: read the resident range back, allocating nothing
       return;
     }
     void *d = nullptr;
     if (gs_probe_mem_alloc(g.probe, bytes, &d) != GS_OK) {
       logv(1, "health probe skipped: %s", gs_cuda_last_error());
-      sentinel_check(idx, g);
+      sentinel_check(g);
       return;
     }
     gs_slice s;
@@ -334,12 +350,13 @@ struct ProbeWorker {
     }
     g.inflight = true;
     g.inflight_is_health = true;
+    g.health_tick = tick;
   }
   // A GPU granted out to the last unit leaves the health checker nothing to allocate. A small range
   // taken and written once while the GPU was still empty is read back instead through the entry
   // point that allocates nothing (gs_probe_verify_noalloc): the whole path -- launch, loads from
   // HBM, compare, verdict -- still answers, and the range itself must still hold what was written.
-  void sentinel_setup(int idx, Gpu &g) {
+  void sentinel_setup(Gpu &g) {
     void *d = nullptr;
     if (gs_probe_mem_alloc(g.probe, kSentinelBytes, &d) != GS_OK) return;
     gs_slice s;
@@ -350,14 +367,14 @@ struct ProbeWorker {
     s.pattern = GS_PROBE_PATTERN_HASH;
     gs_slice_result r;
     if (gs_probe_run(g.probe, &s, 1, GS_PROBE_WRITE | GS_PROBE_VERIFY, &r, nullptr) != GS_OK || r.mismatches) {
-      logv(1, "health probe: gpu %d: sentinel range could not be written", idx);
+      logv(1, "health probe: gpu %d: sentinel range could not be written", g.index);
       gs_probe_mem_free(g.probe, d);
       return;
     }
     g.sentinel = d;
     g.sentinel_seed = s.seed;
   }
-  void sentinel_check(int idx, Gpu &g) {
+  void sentinel_check(Gpu &g) {
     if (!g.sentinel) return;
     gs_slice s;
     memset(&s, 0, sizeof(s));
@@ -368,31 +385,34 @@ struct ProbeWorker {
     gs_slice_result r;
     const int rc = gs_probe_verify_noalloc(g.cuda_ordinal, nullptr, &s, 1, &r);
     if (rc != GS_OK) {
-      logv(1, "health probe: gpu %d: %s", idx, gs_cuda_last_error());
+      logv(1, "health probe: gpu %d: %s", g.index, gs_cuda_last_error());
       return;
     }
-    logv(1, "health probe: gpu %d sentinel of %llu bytes read back without allocating, %llu mismatching words", idx,
-         (unsigned long long)kSentinelBytes, (unsigned long long)r.mismatches);
-    if (r.mismatches) mark_bad(idx);
+    logv(1, "health probe: gpu %d sentinel of %llu bytes read back without allocating, %llu mismatching words",
+         g.index, (unsigned long long)kSentinelBytes, (unsigned long long)r.mismatches);
+    if (r.mismatches) mark_bad(g.index);
   }
-  void run() {
-    for (auto &kv : gpus) sentinel_setup(kv.first, kv.second);
-    time_t last = time(nullptr);
+  void run(Gpu &g) {
+    sentinel_setup(g);
+    long ticks_done = 0;
     while (!stop.load()) {
-      bool busy = false;
-      for (auto &kv : gpus) busy |= kv.second.inflight || !kv.second.pending.empty();
+      const bool busy = g.inflight || !g.pending.empty();
+      // the next health tick of every GPU falls on the same instant: epoch + k * interval
+      auto wake = Clock::now() + std::chrono::milliseconds(busy ? 2 : 200);
+      Clock::time_point next_tick{};
+      if (health_interval > 0) {
+        next_tick = epoch + std::chrono::seconds(health_interval * (ticks_done + 1));
+        if (next_tick < wake) wake = next_tick;
+      }
       {
-        std::unique_lock<std::mutex> lk(mu);
+        std::unique_lock<std::mutex> lk(g.mu);
         // while a sweep is in flight come back soon to collect it; otherwise sleep until a grant arrives
-        cv.wait_for(lk, std::chrono::milliseconds(busy ? 2 : 200), [&] { return stop.load() || !queue.empty(); });
-        while (!queue.empty()) {
-          const ProbeJob j = queue.front();
-          queue.pop_front();
-          auto it = gpus.find(j.gpu);
-          if (it == gpus.end()) continue;
-          Gpu &g = it->second;
-          g.recent_grants.emplace_back(std::chrono::steady_clock::now(), j.bytes);
-          if (g.pending.empty()) g.first_pending = std::chrono::steady_clock::now();
+        g.cv.wait_until(lk, wake, [&] { return stop.load() || !g.queue.empty(); });
+        while (!g.queue.empty()) {
+          const ProbeJob j = g.queue.front();
+          g.queue.pop_front();
+          g.recent_grants.emplace_back(Clock::now(), j.bytes);
+          if (g.pending.empty()) g.first_pending = Clock::now();
           if (g.pending.size() >= GS_PROBE_MAX_SLICES) {  // HBM cannot be swept as fast as it is granted:
             g.pending.pop_front();                        // the newest grants win, the rest are counted
             ++g.dropped;
@@ -400,26 +420,47 @@ struct ProbeWorker {
           g.pending.push_back(j);
         }
       }
-      for (auto &kv : gpus) harvest(kv.first, kv.second, false);
-      for (auto &kv : gpus) start_grants(kv.first, kv.second);
-      if (health_interval > 0 && time(nullptr) - last >= health_interval) {
-        last = time(nullptr);
-        for (auto &kv : gpus) start_health(kv.first, kv.second);
+      harvest(g, false);
+      start_grants(g);
+      if (health_interval > 0 && Clock::now() >= next_tick) {
+        // ticks missed while a long sweep ran are skipped, not queued up
+        while (epoch + std::chrono::seconds(health_interval * (ticks_done + 1)) <= Clock::now()) ++ticks_done;
+        start_health(g, epoch + std::chrono::seconds(health_interval * ticks_done));
       }
     }
+    harvest(g, true);
+    if (g.sentinel) gs_probe_mem_free(g.probe, g.sentinel);
+    gs_probe_close(g.probe);
+    g.probe = nullptr;
+  }
+  void start() {
+    epoch = Clock::now();
     for (auto &kv : gpus) {
-      Gpu &g = kv.second;
-      harvest(kv.first, g, true);
-      if (g.sentinel) gs_probe_mem_free(g.probe, g.sentinel);
-      gs_probe_close(g.probe);
+      Gpu *g = kv.second.get();
+      g->th = std::thread([this, g] { run(*g); });
+    }
+  }
+  void shutdown() {
+    stop.store(true);
+    for (auto &kv : gpus) {
+      {
+        std::lock_guard<std::mutex> lk(kv.second->mu);
+      }
+      kv.second->cv.notify_all();
+    }
+    for (auto &kv : gpus) {
+      if (kv.second->th.joinable()) kv.second->th.join();
+      else if (kv.second->probe) gs_probe_close(kv.second->probe);  // never started: nothing else owns it
     }
   }
   void push(const ProbeJob &j) {
+    auto it = gpus.find(j.gpu);
+    if (it == gpus.end()) return;
     {
-      std::lock_guard<std::mutex> lk(mu);
-      queue.push_back(j);
+      std::lock_guard<std::mutex> lk(it->second->mu);
+      it->second->queue.push_back(j);
     }
-    cv.notify_one();
+    it->second->cv.notify_one();
   }
 };
 
@@ -592,7 +633,7 @@ struct PluginInstance {
       }
     }
     *resp_len = res.resp_len;
-    if (rc == GS_OK && res.kind == GS_ALLOC_MATCHED && probes && probes->gpus.count(res.gpu_index))
+    if (rc == GS_OK && res.kind == GS_ALLOC_MATCHED && probes && probes->has(res.gpu_index))
       probes->push(ProbeJob{res.gpu_index, res.pod_req_units * unit_bytes, res.pod_index});
     return rc;
   }
@@ -624,7 +665,7 @@ struct PluginInstance {
       }
       logv(1, "Registered device plugin with Kubelet");
     }
-    if (probes) probes->th = std::thread([this] { probes->run(); });
+    if (probes) probes->start();
     if (f.health_check) {
       uint64_t bad_mask = 0;
       if (gs_health_open(&bad_mask) == GS_OK) {
@@ -670,11 +711,7 @@ struct PluginInstance {
     if (health_thread.joinable()) health_thread.join();
     if (health_open) gs_health_close();
     if (probes) {
-      probes->stop.store(true);
-      probes->cv.notify_all();
-      if (probes->th.joinable()) probes->th.join();
-      else
-        for (auto &kv : probes->gpus) gs_probe_close(kv.second.probe);
+      probes->shutdown();
       probes.reset();
     }
     if (plugin) gs_plugin_free(plugin);

@@ -208,3 +208,31 @@ def test_scheduler_sweep_catches_a_store_pass_that_did_nothing():
             assert a != b
         finally:
             p.free(arena)
+
+
+def test_daemon_health_sweeps_run_on_all_gpus_at_once(tmp_path):
+    """A node's health-time sweep takes about one GPU's time, not the sum: every GPU has its own
+    worker thread, the ticks fall on the same instant, and allocation, sweep and release of one GPU
+    overlap with those of the others. Needs two GPUs or more."""
+    import re
+    import time
+
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("one GPU: nothing to overlap")
+    proc, sock = _start_daemon(tmp_path, [], interval=3)
+    try:
+        time.sleep(11)                                   # three ticks
+    finally:
+        err = _stop_daemon(proc)
+    assert proc.returncode == 0, err[-2000:]
+    done = [(int(g), float(ms)) for g, ms in re.findall(r"health probe: gpu (\d+) done (\d+) ms after the tick", err)]
+    assert len(done) >= 2 * n, err[-3000:]
+    last_round = dict(done[-n:])                         # the last tick: one line per GPU
+    assert sorted(last_round) == list(range(n)), done
+    fastest, slowest = min(last_round.values()), max(last_round.values())
+    # run one after the other the slowest would finish n times later than the fastest
+    assert slowest < 1.6 * fastest + 150, last_round
+    swept = re.findall(r"health probe: gpu \d+ swept (\d+) bytes .* (\d+) mismatching words", err)
+    assert swept and all(int(m) == 0 and int(b) > 100 << 30 for b, m in swept)
