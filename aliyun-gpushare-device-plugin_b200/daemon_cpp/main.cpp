@@ -162,7 +162,8 @@ Flags parse_flags(int argc, char **argv) {
 // smaller than the L2 can hide), submits it and goes on; finished batches are collected by polling.
 // Health-time sweeps of free memory fire on every GPU at the same instant (the ticks are counted
 // from one shared epoch), each on its own thread -- allocation, sweep and release included -- so a
-// node's sweep takes one GPU's time, not the sum. Every sweep draws its seeds from the engine
+// node's sweep takes far less than the sum (8 B200s: 0.73 s against 8 x 0.36 s; the driver
+// serialises part of each allocation, the sweeps overlap). Every sweep draws its seeds from the engine
 // (gs_probe_next_seed): what an earlier sweep left in a range never matches.
 struct ProbeJob {
   int gpu;
