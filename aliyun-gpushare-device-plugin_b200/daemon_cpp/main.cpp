@@ -441,7 +441,7 @@ struct ProbeWorker {
       g->th = std::thread([this, g] { run(*g); });
     }
   }
-  void shutdown() {
+  void shutdown() {  // idempotent
     stop.store(true);
     for (auto &kv : gpus) {
       {
@@ -450,10 +450,15 @@ struct ProbeWorker {
       kv.second->cv.notify_all();
     }
     for (auto &kv : gpus) {
-      if (kv.second->th.joinable()) kv.second->th.join();
-      else if (kv.second->probe) gs_probe_close(kv.second->probe);  // never started: nothing else owns it
+      if (kv.second->th.joinable()) {
+        kv.second->th.join();  // the thread closed its engine on the way out
+      } else if (kv.second->probe) {
+        gs_probe_close(kv.second->probe);  // never started: nothing else owns it
+        kv.second->probe = nullptr;
+      }
     }
   }
+  ~ProbeWorker() { shutdown(); }
   void push(const ProbeJob &j) {
     auto it = gpus.find(j.gpu);
     if (it == gpus.end()) return;
